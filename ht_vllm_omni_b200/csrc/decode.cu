@@ -1,0 +1,655 @@
+// decode.cu — Kernel 2: persistent split-KV paged flash-decoding for sm_100a.
+//
+// Reference semantics: the decode branch of AttentionImpl.forward, i.e. kernel_unified_attention
+// ($VLLM/v1/attention/ops/triton_unified_attention.py:440-643: paged gather by block_table, S = scale*Q.K^T,
+// seq_len mask, online softmax, P.V, split-KV partial store) with the FlashInfer scale convention
+// ($VLLM/v1/attention/backends/flashinfer.py:1396-1404: k_scale folded into the logit scale, v_scale applied
+// to the output).
+//
+// Design:
+//   * Work = flat list of (sequence, kv head, 64-token tile); the plan kernel cuts it into equal contiguous
+//     ranges, one per persistent CTA, so ragged batches stay balanced.  A CTA walks its range as "segments"
+//     (maximal runs inside one (sequence, kv head)).
+//   * Warp 4 is the producer: it issues TMA tensor loads (UTMALDG, 128B swizzle, L2 evict-first) of 16-token x
+//     128-byte boxes straight out of the paged cache into a ring of smem stages, and a bulk copy of the G query
+//     rows of each segment.  mbarrier full/empty pairs, no __syncthreads in the steady state.
+//   * Warps 0-3 are consumers; each owns one 16-token chunk of every stage:
+//       S(16 heads x 16 tok) = Q.K^T on mma.sync m16n8k16 (heads are the M rows, padded to 16),
+//       online softmax in registers (log2 domain), P reused as the B operand of O^T(128 x heads) += V^T.P^T.
+//     FP8 K/V bytes are expanded e4m3 -> f16 in registers (exact, F2FP.UNPACK) right before the HMMA; the
+//     byte gather that transposes V uses PRMT.  16-bit K/V feed the HMMA directly (V through LDSM.T).
+//   * Segment end: the 4 warps combine their (m, l, O) through smem; a segment that covers the whole
+//     sequence is normalised and stored to `out`, otherwise the partial goes to the workspace for merge.cu.
+#include "common.cuh"
+
+namespace b200attn {
+
+struct DecodeParams {
+  const void* q;
+  int64_t q_stride_t, q_stride_h;
+  void* out;
+  int64_t out_stride_t, out_stride_h;
+  const int32_t* block_table;
+  int64_t bt_stride;
+  const int32_t* seq_lens;
+  const int32_t* plan;
+  float* ws_o;
+  float* ws_ml;
+  const float* k_scale;
+  const float* v_scale;
+  float* lse_out;
+  float sm_scale_log2;  // sm_scale * log2(e)
+  int scale_stride;
+  int B, Hq, Hv;        // Hv = virtual kv heads = Hkv * gsplit
+  int G;                // query heads per virtual kv head (<= 16)
+  int gsplit;           // virtual heads per physical kv head
+  int cpb;              // 16-token chunks per cache block (block_size / 16)
+};
+
+constexpr int kD = 128;
+constexpr int kQSlotBytes = kMaxGroup * kD * 2;  // 4 KiB: 16 query rows
+constexpr int kRedStride = kD + 4;               // floats; +4 keeps rows 16-byte aligned and staggers banks
+
+template <int KVT>
+struct KvCfg {
+  static constexpr bool kFp8 = (KVT == B200ATTN_FP8_E4M3);
+  static constexpr int kChunkBytes = kChunkTokens * kD * (kFp8 ? 1 : 2);  // 2 KiB / 4 KiB
+  static constexpr int kStageBytes = kChunkBytes * kConsumerWarps * 2;    // K + V: 16 KiB / 32 KiB
+};
+
+// smem carve-up, shared by host (size) and device (offsets)
+template <int KVT, int NT>
+struct Smem {
+  static constexpr int kStageBytes = KvCfg<KVT>::kStageBytes;
+  static constexpr int kRedOBytes = kConsumerWarps * NT * 8 * kRedStride * 4;
+  static constexpr int kRedMlBytes = kConsumerWarps * kMaxGroup * 2 * 4;
+  static constexpr int kDescBytes = 2 * 32;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kFixedBytes = 2 * kQSlotBytes + kRedOBytes + kRedMlBytes + kDescBytes + kBarBytes;
+  // fp8: 2 CTAs / SM (113 KiB each); 16-bit: 1 CTA / SM (227 KiB)
+  static constexpr int kCtas = KvCfg<KVT>::kFp8 ? 2 : 1;
+  static constexpr int kBudget = kCtas == 2 ? 113 * 1024 : 227 * 1024;
+  static constexpr int kStagesRaw = (kBudget - kFixedBytes - 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kTotalBytes = kStages * kStageBytes + kFixedBytes + 1024;  // +1024: manual alignment
+  static_assert(kStages >= 3, "pipeline too shallow");
+};
+
+template <int QDT>
+__device__ __forceinline__ float q_to_float(uint16_t raw) {
+  if constexpr (QDT == B200ATTN_BF16) return __uint_as_float((uint32_t)raw << 16);
+  else return __half2float(__ushort_as_half(raw));
+}
+
+template <int KVT, int QDT, int NT>
+__global__ void __launch_bounds__(kDecodeThreads, Smem<KVT, NT>::kCtas)
+decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v, const DecodeParams p) {
+  using Cfg = KvCfg<KVT>;
+  using SM = Smem<KVT, NT>;
+  constexpr bool kFp8 = Cfg::kFp8;
+  constexpr bool kMmaBf16 = !kFp8 && (KVT == B200ATTN_BF16);  // HMMA operand type (fp8 is expanded to f16)
+  constexpr int kStages = SM::kStages;
+  constexpr int kChunkBytes = Cfg::kChunkBytes;
+  constexpr int kStageBytes = Cfg::kStageBytes;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t stages_base = smem_base;
+  const uint32_t q_base = stages_base + kStages * kStageBytes;
+  const uint32_t redo_base = q_base + 2 * kQSlotBytes;
+  const uint32_t redml_base = redo_base + SM::kRedOBytes;
+  const uint32_t desc_base = redml_base + SM::kRedMlBytes;
+  const uint32_t bar_base = desc_base + SM::kDescBytes;
+  // generic pointers for the small reduction buffers
+  uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+  float* red_o = reinterpret_cast<float*>(smem_al + (redo_base - smem_base));
+  float* red_ml = reinterpret_cast<float*>(smem_al + (redml_base - smem_base));
+  volatile int* desc = reinterpret_cast<volatile int*>(smem_al + (desc_base - smem_base));
+  auto full_bar = [&](uint32_t s) { return bar_base + s * 8; };
+  auto empty_bar = [&](uint32_t s) { return bar_base + (kStages + s) * 8; };
+  auto qfull_bar = [&](uint32_t s) { return bar_base + (2 * kStages + s) * 8; };
+  auto qempty_bar = [&](uint32_t s) { return bar_base + (2 * kStages + 2 + s) * 8; };
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), kConsumerWarps);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(qfull_bar(s), 1);
+      mbar_init(qempty_bar(s), kConsumerWarps);
+    }
+    mbar_fence_init();
+    prefetch_tensormap(&tm_k);
+    prefetch_tensormap(&tm_v);
+  }
+  __syncthreads();
+
+  // Everything above overlaps the tail of the preceding kernel (KV write / plan); from here on we read
+  // memory it produced.
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int4 cs = __ldg(reinterpret_cast<const int4*>(p.plan + kPlanHeaderWords) + blockIdx.x);
+  if (cs.x < 0 || cs.w <= 0) return;  // idle CTA (fewer tiles than CTAs)
+
+  if (warp == kConsumerWarps) {
+    // =========================================== producer ===========================================
+    const uint64_t pol = policy_evict_first();
+    int s = cs.x, hv = cs.y, tile = cs.z, remaining = cs.w;
+    uint32_t stage = 0, phase = 0, sg = 0;
+    const uint16_t* qptr = reinterpret_cast<const uint16_t*>(p.q);
+    while (remaining > 0) {
+      const int L = __ldg(p.seq_lens + s);
+      const int nt = (L + kTileTokens - 1) / kTileTokens;
+      const int n = min(remaining, nt - tile);
+      // ---- query rows of this segment + its descriptor ----
+      const uint32_t slot = sg & 1;
+      mbar_wait(qempty_bar(slot), ((sg >> 1) & 1) ^ 1);
+      if (lane == 0) {
+        volatile int* d = desc + slot * 8;
+        d[0] = s; d[1] = hv; d[2] = tile; d[3] = n; d[4] = L;
+        mbar_arrive_expect_tx(qfull_bar(slot), (uint32_t)p.G * kD * 2);
+      }
+      __syncwarp();
+      if (lane < p.G) {
+        const uint16_t* src = qptr + (int64_t)s * p.q_stride_t + (int64_t)(hv * p.G + lane) * p.q_stride_h;
+        bulk_load_1d(q_base + slot * kQSlotBytes + lane * (kD * 2), src, kD * 2, qfull_bar(slot));
+      }
+      // ---- K/V tiles ----
+      const int kvh = hv / p.gsplit;
+      const int32_t* bt = p.block_table + (int64_t)s * p.bt_stride;
+      int blk = 0;
+      for (int tt = 0; tt < n; ++tt) {
+        const int tl = tile + tt;
+        if ((tt & 7) == 0) {  // refill 32 block ids (8 tiles) with one coalesced load
+          const int ci = (tl << 2) + lane;
+          blk = (ci * kChunkTokens < L) ? __ldg(bt + ci / p.cpb) : 0;
+        }
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        const int tok0 = tl * kTileTokens;
+        const int nvalid = min(kConsumerWarps, (L - tok0 + kChunkTokens - 1) / kChunkTokens);
+        if (lane == 0) mbar_arrive_expect_tx(full_bar(stage), (uint32_t)nvalid * 2 * kChunkBytes);
+        __syncwarp();
+        const int c = (lane >> 1) & 3;
+        const int kv = lane & 1;
+        const int b = __shfl_sync(0xffffffffu, blk, ((tt & 7) << 2) + c);
+        if (lane < 8 && c < nvalid) {
+          const int ci = (tl << 2) + c;
+          const int row0 = (ci % p.cpb) * kChunkTokens;
+          const uint32_t dst = stages_base + stage * kStageBytes + (kv ? kConsumerWarps * kChunkBytes : 0) + c * kChunkBytes;
+          const CUtensorMap* tm = kv ? &tm_v : &tm_k;
+          if constexpr (kFp8) {
+            tma_load_4d(dst, tm, full_bar(stage), 0, row0, kvh, b, pol);
+          } else {
+            tma_load_4d(dst, tm, full_bar(stage), 0, row0, kvh, b, pol);
+            tma_load_4d(dst + 2048, tm, full_bar(stage), 64, row0, kvh, b, pol);
+          }
+        }
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+      remaining -= n;
+      tile += n;
+      ++sg;
+      if (tile == nt) {
+        tile = 0;
+        if (++hv == p.Hv) {
+          hv = 0;
+          do { ++s; } while (s < p.B && remaining > 0 && __ldg(p.seq_lens + s) <= 0);
+          if (s >= p.B) break;
+        }
+      }
+    }
+    return;
+  }
+
+  // ============================================= consumers =============================================
+  const int w = warp;
+  const int g = lane >> 2;
+  const int t = lane & 3;
+  const int tid = threadIdx.x;  // 0..127
+  int remaining = cs.w;
+  uint32_t stage = 0, phase = 0, sg = 0;
+  const float ninf = -INFINITY;
+
+  while (remaining > 0) {
+    const uint32_t slot = sg & 1;
+    mbar_wait(qfull_bar(slot), (sg >> 1) & 1);
+    const int s = desc[slot * 8 + 0];
+    const int hv = desc[slot * 8 + 1];
+    const int tile0 = desc[slot * 8 + 2];
+    const int n = desc[slot * 8 + 3];
+    const int L = desc[slot * 8 + 4];
+    const int kvh = hv / p.gsplit;
+
+    // ---- Q fragments (A operand: rows = heads g / g+8, k = permuted head-dim) ----
+    uint32_t qa[8][4];
+    float crow_lo, crow_hi;
+    {
+      const float kscale = kFp8 ? __ldg(p.k_scale + (int64_t)kvh * p.scale_stride) : 1.0f;
+      const uint32_t qs = q_base + slot * kQSlotBytes;
+      const bool lo_ok = g < p.G;
+      const bool hi_ok = (NT == 2) && (g + 8 < p.G);
+      uint2 rlo[8], rhi[8];
+#pragma unroll
+      for (int st = 0; st < 8; ++st) {
+        const int dbase = kFp8 ? (32 * t + 4 * st) : (64 * (st >> 2) + 16 * t + 4 * (st & 3));
+        rlo[st] = lo_ok ? lds64(qs + g * (kD * 2) + dbase * 2) : make_uint2(0u, 0u);
+        rhi[st] = hi_ok ? lds64(qs + (g + 8) * (kD * 2) + dbase * 2) : make_uint2(0u, 0u);
+      }
+      float f_lo = 1.0f, f_hi = 1.0f;  // factor folded back into the logit scale
+      if constexpr (kFp8 && QDT == B200ATTN_BF16) {
+        // bf16 -> f16 with an exact per-row power-of-two pre-scale (keeps any finite bf16 row in f16 range)
+        float amax_lo = 0.f, amax_hi = 0.f;
+#pragma unroll
+        for (int st = 0; st < 8; ++st) {
+          amax_lo = fmaxf(amax_lo, fmaxf(fmaxf(fabsf(q_to_float<QDT>(rlo[st].x & 0xffff)), fabsf(q_to_float<QDT>(rlo[st].x >> 16))),
+                                         fmaxf(fabsf(q_to_float<QDT>(rlo[st].y & 0xffff)), fabsf(q_to_float<QDT>(rlo[st].y >> 16)))));
+          amax_hi = fmaxf(amax_hi, fmaxf(fmaxf(fabsf(q_to_float<QDT>(rhi[st].x & 0xffff)), fabsf(q_to_float<QDT>(rhi[st].x >> 16))),
+                                         fmaxf(fabsf(q_to_float<QDT>(rhi[st].y & 0xffff)), fabsf(q_to_float<QDT>(rhi[st].y >> 16)))));
+        }
+        amax_lo = fmaxf(amax_lo, __shfl_xor_sync(0xffffffffu, amax_lo, 1));
+        amax_lo = fmaxf(amax_lo, __shfl_xor_sync(0xffffffffu, amax_lo, 2));
+        amax_hi = fmaxf(amax_hi, __shfl_xor_sync(0xffffffffu, amax_hi, 1));
+        amax_hi = fmaxf(amax_hi, __shfl_xor_sync(0xffffffffu, amax_hi, 2));
+        const uint32_t eb_lo = (__float_as_uint(amax_lo) >> 23) & 0xffu;
+        const uint32_t eb_hi = (__float_as_uint(amax_hi) >> 23) & 0xffu;
+        // inv = 2^(8-e) puts the row maximum in [256, 512); f = 2^(e-8) undoes it on the logits.  Rows whose
+        // maximum is below 2^-111 (biased exponent < 16) are left alone: their logits are ~0 either way.
+        const float inv_lo = eb_lo >= 16 ? __uint_as_float((262u - eb_lo) << 23) : 1.0f;
+        const float inv_hi = eb_hi >= 16 ? __uint_as_float((262u - eb_hi) << 23) : 1.0f;
+        f_lo = eb_lo >= 16 ? __uint_as_float((eb_lo - 8u) << 23) : 1.0f;
+        f_hi = eb_hi >= 16 ? __uint_as_float((eb_hi - 8u) << 23) : 1.0f;
+#pragma unroll
+        for (int st = 0; st < 8; ++st) {
+          qa[st][0] = pack_f32x2<false>(q_to_float<QDT>(rlo[st].x & 0xffff) * inv_lo, q_to_float<QDT>(rlo[st].x >> 16) * inv_lo);
+          qa[st][2] = pack_f32x2<false>(q_to_float<QDT>(rlo[st].y & 0xffff) * inv_lo, q_to_float<QDT>(rlo[st].y >> 16) * inv_lo);
+          qa[st][1] = pack_f32x2<false>(q_to_float<QDT>(rhi[st].x & 0xffff) * inv_hi, q_to_float<QDT>(rhi[st].x >> 16) * inv_hi);
+          qa[st][3] = pack_f32x2<false>(q_to_float<QDT>(rhi[st].y & 0xffff) * inv_hi, q_to_float<QDT>(rhi[st].y >> 16) * inv_hi);
+        }
+      } else {
+#pragma unroll
+        for (int st = 0; st < 8; ++st) {
+          qa[st][0] = rlo[st].x; qa[st][2] = rlo[st].y;
+          qa[st][1] = rhi[st].x; qa[st][3] = rhi[st].y;
+        }
+      }
+      crow_lo = f_lo * p.sm_scale_log2 * kscale;
+      crow_hi = f_hi * p.sm_scale_log2 * kscale;
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(qempty_bar(slot));
+
+    float m_lo = ninf, m_hi = ninf, l_lo = 0.f, l_hi = 0.f;
+    float o[NT][8][4];
+#pragma unroll
+    for (int a = 0; a < NT; ++a)
+#pragma unroll
+      for (int b = 0; b < 8; ++b)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) o[a][b][c] = 0.f;
+
+    for (int tt = 0; tt < n; ++tt) {
+      mbar_wait(full_bar(stage), phase);
+      const int tok0 = (tile0 + tt) * kTileTokens + w * kChunkTokens;
+      if (tok0 < L) {
+        const uint32_t kbase = stages_base + stage * kStageBytes + w * kChunkBytes;
+        const uint32_t vbase = kbase + kConsumerWarps * kChunkBytes;
+        const bool partial = tok0 + kChunkTokens > L;
+
+        // ---------------- S = Q.K^T : two 8-token n-tiles (sA: tokens 0-7, sB: tokens 8-15) ----------------
+        float sA[4] = {0.f, 0.f, 0.f, 0.f}, sB[4] = {0.f, 0.f, 0.f, 0.f};
+        if constexpr (kFp8) {
+          const uint32_t rA = kbase + g * 128, rB = kbase + (g + 8) * 128;
+          const uint32_t c0 = (uint32_t)((2 * t) ^ g) << 4, c1 = (uint32_t)((2 * t + 1) ^ g) << 4;
+          const uint4 ka0 = lds128(rA + c0), ka1 = lds128(rA + c1);
+          const uint4 kb0 = lds128(rB + c0), kb1 = lds128(rB + c1);
+          const uint32_t kaw[8] = {ka0.x, ka0.y, ka0.z, ka0.w, ka1.x, ka1.y, ka1.z, ka1.w};
+          const uint32_t kbw[8] = {kb0.x, kb0.y, kb0.z, kb0.w, kb1.x, kb1.y, kb1.z, kb1.w};
+#pragma unroll
+          for (int st = 0; st < 8; ++st) {
+            mma_16816<false>(sA, qa[st][0], qa[st][1], qa[st][2], qa[st][3], e4m3x2_to_f16x2_lo(kaw[st]), e4m3x2_to_f16x2_hi(kaw[st]));
+            mma_16816<false>(sB, qa[st][0], qa[st][1], qa[st][2], qa[st][3], e4m3x2_to_f16x2_lo(kbw[st]), e4m3x2_to_f16x2_hi(kbw[st]));
+          }
+        } else {
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+              const uint32_t co = (uint32_t)((2 * t + i) ^ g) << 4;
+              const uint4 ka = lds128(kbase + hf * 2048 + g * 128 + co);
+              const uint4 kb = lds128(kbase + hf * 2048 + (g + 8) * 128 + co);
+              const int st = hf * 4 + i * 2;
+              mma_16816<kMmaBf16>(sA, qa[st][0], qa[st][1], qa[st][2], qa[st][3], ka.x, ka.y);
+              mma_16816<kMmaBf16>(sA, qa[st + 1][0], qa[st + 1][1], qa[st + 1][2], qa[st + 1][3], ka.z, ka.w);
+              mma_16816<kMmaBf16>(sB, qa[st][0], qa[st][1], qa[st][2], qa[st][3], kb.x, kb.y);
+              mma_16816<kMmaBf16>(sB, qa[st + 1][0], qa[st + 1][1], qa[st + 1][2], qa[st + 1][3], kb.z, kb.w);
+            }
+          }
+        }
+
+        // ---------------- online softmax (log2 domain) ----------------
+        // thread (g,t) holds S[head g][tok 2t,2t+1] in s?[0..1] and S[head g+8][..] in s?[2..3]
+        float x[8];
+        x[0] = sA[0] * crow_lo; x[1] = sA[1] * crow_lo; x[2] = sB[0] * crow_lo; x[3] = sB[1] * crow_lo;
+        x[4] = sA[2] * crow_hi; x[5] = sA[3] * crow_hi; x[6] = sB[2] * crow_hi; x[7] = sB[3] * crow_hi;
+        if (partial) {
+          const int j0 = tok0 + 2 * t;
+          if (j0 >= L) { x[0] = ninf; x[4] = ninf; }
+          if (j0 + 1 >= L) { x[1] = ninf; x[5] = ninf; }
+          if (j0 + 8 >= L) { x[2] = ninf; x[6] = ninf; }
+          if (j0 + 9 >= L) { x[3] = ninf; x[7] = ninf; }
+        }
+        float mx_lo = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
+        mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 1));
+        mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 2));
+        float mx_hi = ninf;
+        if constexpr (NT == 2) {
+          mx_hi = fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7]));
+          mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 1));
+          mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 2));
+        }
+        const bool grow = (mx_lo > m_lo) || (NT == 2 && mx_hi > m_hi);
+        if (__any_sync(0xffffffffu, grow)) {
+          const float mn_lo = fmaxf(m_lo, mx_lo);
+          const float al_lo = fast_exp2(m_lo - mn_lo);  // m_lo = -inf -> 0
+          l_lo *= al_lo;
+          m_lo = mn_lo;
+          // O^T accumulators carry heads along t: fetch alpha of heads 2t and 2t+1
+          const float a0 = __shfl_sync(0xffffffffu, al_lo, (2 * t) << 2);
+          const float a1 = __shfl_sync(0xffffffffu, al_lo, (2 * t + 1) << 2);
+#pragma unroll
+          for (int mt = 0; mt < 8; ++mt) {
+            o[0][mt][0] *= a0; o[0][mt][1] *= a1; o[0][mt][2] *= a0; o[0][mt][3] *= a1;
+          }
+          if constexpr (NT == 2) {
+            const float mn_hi = fmaxf(m_hi, mx_hi);
+            const float al_hi = fast_exp2(m_hi - mn_hi);
+            l_hi *= al_hi;
+            m_hi = mn_hi;
+            const float b0 = __shfl_sync(0xffffffffu, al_hi, (2 * t) << 2);
+            const float b1 = __shfl_sync(0xffffffffu, al_hi, (2 * t + 1) << 2);
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) {
+              o[1][mt][0] *= b0; o[1][mt][1] *= b1; o[1][mt][2] *= b0; o[1][mt][3] *= b1;
+            }
+          }
+        }
+        uint32_t pb[NT][2];
+        {
+          const float p0 = fast_exp2(x[0] - m_lo), p1 = fast_exp2(x[1] - m_lo);
+          const float p2 = fast_exp2(x[2] - m_lo), p3 = fast_exp2(x[3] - m_lo);
+          l_lo += (p0 + p1) + (p2 + p3);
+          pb[0][0] = pack_f32x2<kMmaBf16>(p0, p1);
+          pb[0][1] = pack_f32x2<kMmaBf16>(p2, p3);
+          if constexpr (NT == 2) {
+            // rows g+8 >= G hold zero queries: their m/l/o are never stored, exp2(0 - 0) = 1 is harmless
+            const float q0 = fast_exp2(x[4] - m_hi), q1 = fast_exp2(x[5] - m_hi);
+            const float q2 = fast_exp2(x[6] - m_hi), q3 = fast_exp2(x[7] - m_hi);
+            l_hi += (q0 + q1) + (q2 + q3);
+            pb[1][0] = pack_f32x2<kMmaBf16>(q0, q1);
+            pb[1][1] = pack_f32x2<kMmaBf16>(q2, q3);
+          }
+        }
+
+        // ---------------- O^T(d x heads) += V^T(d x tok) . P^T(tok x heads) ----------------
+        if constexpr (kFp8) {
+          // thread owns the 16 head-dims [16g, 16g+16) of tokens {2t, 2t+1, 2t+8, 2t+9}
+          const uint32_t cg = (uint32_t)g;
+          uint4 v0 = lds128(vbase + (2 * t) * 128 + ((cg ^ (uint32_t)(2 * t)) << 4));
+          uint4 v1 = lds128(vbase + (2 * t + 1) * 128 + ((cg ^ (uint32_t)(2 * t + 1)) << 4));
+          uint4 v2 = lds128(vbase + (2 * t + 8) * 128 + ((cg ^ (uint32_t)(2 * t)) << 4));
+          uint4 v3 = lds128(vbase + (2 * t + 9) * 128 + ((cg ^ (uint32_t)(2 * t + 1)) << 4));
+          if (partial) {  // never let stale cache bytes (possibly NaN patterns) meet p = 0
+            const int j0 = tok0 + 2 * t;
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            if (j0 >= L) v0 = z;
+            if (j0 + 1 >= L) v1 = z;
+            if (j0 + 8 >= L) v2 = z;
+            if (j0 + 9 >= L) v3 = z;
+          }
+          const uint32_t w0[4] = {v0.x, v0.y, v0.z, v0.w}, w1[4] = {v1.x, v1.y, v1.z, v1.w};
+          const uint32_t w2[4] = {v2.x, v2.y, v2.z, v2.w}, w3[4] = {v3.x, v3.y, v3.z, v3.w};
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+#pragma unroll
+            for (int hb = 0; hb < 2; ++hb) {
+              const uint32_t sel = hb ? 0x7362u : 0x5140u;
+              const uint32_t x01 = __byte_perm(w0[r], w1[r], sel);  // [tok0.d0, tok1.d0, tok0.d1, tok1.d1]
+              const uint32_t x23 = __byte_perm(w2[r], w3[r], sel);
+              const uint32_t a0 = e4m3x2_to_f16x2_lo(x01), a1 = e4m3x2_to_f16x2_hi(x01);
+              const uint32_t a2 = e4m3x2_to_f16x2_lo(x23), a3 = e4m3x2_to_f16x2_hi(x23);
+              mma_16816<false>(o[0][2 * r + hb], a0, a1, a2, a3, pb[0][0], pb[0][1]);
+              if constexpr (NT == 2) mma_16816<false>(o[1][2 * r + hb], a0, a1, a2, a3, pb[1][0], pb[1][1]);
+            }
+          }
+        } else {
+          const int mi = lane >> 3, rr = lane & 7;
+          const uint32_t tokrow = (uint32_t)((mi >> 1) * 8 + rr);
+          uint32_t keep_lo = 0xffffffffu, keep_hi = 0xffffffffu;  // a0/a1 (tok 2t,2t+1), a2/a3 (tok 2t+8,2t+9)
+          if (partial) {
+            const int j0 = tok0 + 2 * t;
+            keep_lo = (j0 < L ? 0x0000ffffu : 0u) | (j0 + 1 < L ? 0xffff0000u : 0u);
+            keep_hi = (j0 + 8 < L ? 0x0000ffffu : 0u) | (j0 + 9 < L ? 0xffff0000u : 0u);
+          }
+#pragma unroll
+          for (int mt = 0; mt < 8; ++mt) {
+            const uint32_t chunk = (uint32_t)(2 * (mt & 3) + (mi & 1));
+            const uint32_t addr = vbase + (mt >> 2) * 2048 + tokrow * 128 + ((chunk ^ (uint32_t)rr) << 4);
+            uint32_t a0, a1, a2, a3;
+            ldmatrix_x4_trans(addr, a0, a1, a2, a3);
+            a0 &= keep_lo; a1 &= keep_lo; a2 &= keep_hi; a3 &= keep_hi;
+            mma_16816<kMmaBf16>(o[0][mt], a0, a1, a2, a3, pb[0][0], pb[0][1]);
+            if constexpr (NT == 2) mma_16816<kMmaBf16>(o[1][mt], a0, a1, a2, a3, pb[1][0], pb[1][1]);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar(stage));
+      if (++stage == kStages) { stage = 0; phase ^= 1; }
+    }
+
+    // ---------------- segment end: combine the 4 warps' (m, l, O) ----------------
+    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 1);
+    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 2);
+    if constexpr (NT == 2) {
+      l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 1);
+      l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 2);
+    }
+    if (t == 0) {
+      red_ml[(w * kMaxGroup + g) * 2 + 0] = m_lo;
+      red_ml[(w * kMaxGroup + g) * 2 + 1] = l_lo;
+      if constexpr (NT == 2) {
+        red_ml[(w * kMaxGroup + g + 8) * 2 + 0] = m_hi;
+        red_ml[(w * kMaxGroup + g + 8) * 2 + 1] = l_hi;
+      }
+    }
+    named_bar_sync(1, kConsumerWarps * 32);
+#pragma unroll
+    for (int a = 0; a < NT; ++a) {
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int head = a * 8 + 2 * t + hh;
+        float mg = ninf;
+#pragma unroll
+        for (int ww = 0; ww < kConsumerWarps; ++ww) mg = fmaxf(mg, red_ml[(ww * kMaxGroup + head) * 2]);
+        const float mine = red_ml[(w * kMaxGroup + head) * 2];
+        const float sc = (mine == ninf) ? 0.f : fast_exp2(mine - mg);
+        float* dst = red_o + ((w * NT * 8) + head) * kRedStride;
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt) {
+          const int dlo = kFp8 ? (16 * g + 2 * mt) : (16 * mt + g);
+          const int dhi = kFp8 ? (dlo + 1) : (dlo + 8);
+          dst[dlo] = o[a][mt][hh] * sc;
+          dst[dhi] = o[a][mt][2 + hh] * sc;
+        }
+      }
+    }
+    named_bar_sync(1, kConsumerWarps * 32);
+    {
+      const bool whole = (tile0 == 0) && ((tile0 + n) * kTileTokens >= L);
+      const int pslot = sg == 0 ? 0 : 1;
+      const float vscale = kFp8 ? __ldg(p.v_scale + (int64_t)kvh * p.scale_stride) : 1.0f;
+      const int d = tid;  // 128 consumer threads <-> 128 head dims
+      for (int head = 0; head < p.G; ++head) {
+        float mg = ninf;
+#pragma unroll
+        for (int ww = 0; ww < kConsumerWarps; ++ww) mg = fmaxf(mg, red_ml[(ww * kMaxGroup + head) * 2]);
+        float lg = 0.f, acc = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < kConsumerWarps; ++ww) {
+          const float mw = red_ml[(ww * kMaxGroup + head) * 2];
+          lg += (mw == ninf) ? 0.f : red_ml[(ww * kMaxGroup + head) * 2 + 1] * fast_exp2(mw - mg);
+          acc += red_o[((ww * NT * 8) + head) * kRedStride + d];
+        }
+        if (whole) {
+          const int hq = hv * p.G + head;
+          using E = Elem<QDT>;
+          typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+          op[d] = E::from_float(acc * (vscale / lg));
+          if (p.lse_out != nullptr && d == 0)
+            p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
+        } else {
+          const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + head;
+          p.ws_o[pidx * kD + d] = acc;
+          if (d == 0) {
+            p.ws_ml[pidx * 2 + 0] = mg;
+            p.ws_ml[pidx * 2 + 1] = lg;
+          }
+        }
+      }
+    }
+    named_bar_sync(1, kConsumerWarps * 32);
+    remaining -= n;
+    ++sg;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+int encode_kv_tensor_map(CUtensorMap* tm, const void* base, int kv_dtype, int64_t stride_block, int64_t stride_slot,
+                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D);
+int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
+int option_force_simt();
+
+template <int KVT, int QDT, int NT>
+static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, cudaStream_t stream) {
+  using SM = Smem<KVT, NT>;
+  auto fn = decode_kernel<KVT, QDT, NT>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kTotalBytes),
+                   "cudaFuncSetAttribute(decode smem)"))
+      return B200ATTN_ECUDA;
+    configured = true;
+  }
+  void* args[] = {(void*)&tk, (void*)&tv, (void*)&p};
+  return launch_with_pdl((const void*)fn, dim3(grid), dim3(kDecodeThreads), SM::kTotalBytes, stream, args);
+}
+
+int decode_smem_bytes(int kv_dtype, int nt) {
+  if (kv_dtype == B200ATTN_FP8_E4M3) return nt == 2 ? Smem<B200ATTN_FP8_E4M3, 2>::kTotalBytes : Smem<B200ATTN_FP8_E4M3, 1>::kTotalBytes;
+  return nt == 2 ? Smem<B200ATTN_BF16, 2>::kTotalBytes : Smem<B200ATTN_BF16, 1>::kTotalBytes;
+}
+
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t,
+                               int64_t out_stride_h, const void* k_cache, const void* v_cache, int64_t stride_block,
+                               int64_t stride_slot, int64_t stride_head, int64_t num_blocks, const int32_t* block_table,
+                               int64_t block_table_stride, const int32_t* seq_lens, int32_t num_seqs, int32_t num_q_heads,
+                               int32_t num_kv_heads, int32_t head_dim, int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
+                               float sm_scale, const float* k_scale, const float* v_scale, int32_t scale_stride,
+                               const void* plan, int32_t num_ctas, void* workspace, size_t workspace_bytes,
+                               float* lse_out, void* stream) {
+  if (num_seqs == 0) return B200ATTN_OK;
+  if (!q || !out || !k_cache || !v_cache || !block_table || !seq_lens || !plan || !workspace) {
+    set_error("decode: null pointer argument");
+    return B200ATTN_EINVAL;
+  }
+  if (head_dim != kD) {
+    set_error("decode: head_dim %d unsupported (only 128)", head_dim);
+    return B200ATTN_EINVAL;
+  }
+  if (block_size <= 0 || block_size % kChunkTokens != 0 || block_size > 256) {
+    set_error("decode: block_size %d must be a multiple of 16 and <= 256", block_size);
+    return B200ATTN_EINVAL;
+  }
+  if (num_kv_heads <= 0 || num_q_heads <= 0 || num_q_heads % num_kv_heads != 0) {
+    set_error("decode: Hq=%d must be a positive multiple of Hkv=%d", num_q_heads, num_kv_heads);
+    return B200ATTN_EINVAL;
+  }
+  if (q_dtype != B200ATTN_BF16 && q_dtype != B200ATTN_FP16) {
+    set_error("decode: q dtype must be bf16 or fp16");
+    return B200ATTN_EINVAL;
+  }
+  const bool fp8 = kv_dtype == B200ATTN_FP8_E4M3;
+  if (!fp8 && kv_dtype != q_dtype) {
+    set_error("decode: 16-bit kv dtype (%d) must equal q dtype (%d)", kv_dtype, q_dtype);
+    return B200ATTN_EINVAL;
+  }
+  if (fp8 && (!k_scale || !v_scale)) {
+    set_error("decode: fp8 cache needs k_scale / v_scale");
+    return B200ATTN_EINVAL;
+  }
+  const int Gfull = num_q_heads / num_kv_heads;
+  int gsplit = 1;
+  while (Gfull / gsplit > kMaxGroup || (Gfull % gsplit) != 0) {
+    ++gsplit;
+    if (gsplit > Gfull) break;
+  }
+  if (gsplit > Gfull || Gfull / gsplit > kMaxGroup) {
+    set_error("decode: cannot tile group size %d into passes of <= %d heads", Gfull, kMaxGroup);
+    return B200ATTN_EINVAL;
+  }
+  const int G = Gfull / gsplit;
+  if (num_ctas <= 0 || num_ctas > kMaxGrid) {
+    set_error("decode: num_ctas %d out of range (1..%d)", num_ctas, kMaxGrid);
+    return B200ATTN_EINVAL;
+  }
+  const size_t need = (ws_o_floats(num_ctas, kD) + ws_ml_floats(num_ctas)) * sizeof(float);
+  if (workspace_bytes < need) {
+    set_error("decode: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+    return B200ATTN_ENOSPACE;
+  }
+  auto mis = [](const void* ptr, int64_t a) { return (reinterpret_cast<uintptr_t>(ptr) % a) != 0; };
+  if (mis(q, 16) || (q_stride_t % 8) || (q_stride_h % 8) || mis(out, 2)) {
+    set_error("decode: q must be 16-byte aligned with strides that are multiples of 8 elements");
+    return B200ATTN_EINVAL;
+  }
+
+  CUtensorMap tk, tv;
+  int rc = encode_kv_tensor_map(&tk, k_cache, kv_dtype, stride_block, stride_slot, stride_head, num_blocks, block_size, num_kv_heads, kD);
+  if (rc) return rc;
+  rc = encode_kv_tensor_map(&tv, v_cache, kv_dtype, stride_block, stride_slot, stride_head, num_blocks, block_size, num_kv_heads, kD);
+  if (rc) return rc;
+
+  DecodeParams p;
+  p.q = q; p.q_stride_t = q_stride_t; p.q_stride_h = q_stride_h;
+  p.out = out; p.out_stride_t = out_stride_t; p.out_stride_h = out_stride_h;
+  p.block_table = block_table; p.bt_stride = block_table_stride;
+  p.seq_lens = seq_lens;
+  p.plan = reinterpret_cast<const int32_t*>(plan);
+  p.ws_o = reinterpret_cast<float*>(workspace);
+  p.ws_ml = p.ws_o + ws_o_floats(num_ctas, kD);
+  p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;
+  p.lse_out = lse_out;
+  p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
+  p.B = num_seqs; p.Hq = num_q_heads; p.Hv = num_kv_heads * gsplit; p.G = G; p.gsplit = gsplit;
+  p.cpb = block_size / kChunkTokens;
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nt = G > 8 ? 2 : 1;
+#define B200_LAUNCH(KVT, QDT)                                                       \
+  (nt == 2 ? launch_decode<KVT, QDT, 2>(tk, tv, p, num_ctas, st) : launch_decode<KVT, QDT, 1>(tk, tv, p, num_ctas, st))
+  if (fp8) return q_dtype == B200ATTN_BF16 ? B200_LAUNCH(B200ATTN_FP8_E4M3, B200ATTN_BF16) : B200_LAUNCH(B200ATTN_FP8_E4M3, B200ATTN_FP16);
+  if (kv_dtype == B200ATTN_BF16) return B200_LAUNCH(B200ATTN_BF16, B200ATTN_BF16);
+  return B200_LAUNCH(B200ATTN_FP16, B200ATTN_FP16);
+#undef B200_LAUNCH
+}

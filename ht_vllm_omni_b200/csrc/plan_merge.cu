@@ -1,0 +1,313 @@
+// plan_merge.cu — the split-KV work plan and Kernel 3 (merge of partial online-softmax results).
+//
+// Reference semantics of the merge: reduce_segments ($VLLM/v1/attention/ops/triton_unified_attention.py:645-733):
+//   m = max_i m_i;  l = sum_i l_i * e^(m_i - m);  o = sum_i o_i * e^(m_i - m) / l
+// and merge_attn_states ($VLLM/v1/attention/ops/merge_attn_states.py:7-101) for the LSE form.
+// Ours works in the log2 domain (m_i are log2-scaled logits) and handles a variable number of partials per
+// (sequence, kv head), located through the plan instead of a fixed segment count.
+#include "common.cuh"
+
+namespace b200attn {
+
+// ------------------------------------------------------------------------------------------------
+// plan: one CTA.  tile_prefix = exclusive scan of ceil(L_s / 64); flat work index x in
+// [0, Hv * tile_prefix[B]) enumerates (s, hv, tile) with tile fastest, then hv, then s.
+// CTA c owns x in [c * tpc, min((c + 1) * tpc, total)).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ seq_lens, int B, int Hv, int grid,
+                                                   int32_t* __restrict__ plan) {
+  __shared__ int warp_sums[8];
+  __shared__ int carry_s;
+  pdl_wait();
+  pdl_launch_dependents();
+  int32_t* prefix = plan + kPlanPrefixOffset;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < B; base += 256) {
+    const int i = base + tid;
+    int nt = 0;
+    if (i < B) {
+      const int L = seq_lens[i];
+      nt = L > 0 ? (L + kTileTokens - 1) / kTileTokens : 0;
+    }
+    int v = nt;  // inclusive warp scan
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, off);
+      if (lane >= off) v += u;
+    }
+    if (lane == 31) warp_sums[wid] = v;
+    __syncthreads();
+    int woff = 0;
+    for (int k = 0; k < wid; ++k) woff += warp_sums[k];
+    const int carry = carry_s;
+    if (i < B) prefix[i] = carry + woff + v - nt;  // exclusive
+    __syncthreads();
+    if (tid == 255) carry_s = carry + woff + v;
+    __syncthreads();
+  }
+  const int total_seq_tiles = carry_s;
+  if (tid == 0) prefix[B] = total_seq_tiles;
+  const long long total = (long long)total_seq_tiles * Hv;
+  const int tpc = total > 0 ? (int)((total + grid - 1) / grid) : 1;
+  if (tid == 0) {
+    plan[0] = (int)total;
+    plan[1] = tpc;
+    plan[2] = grid;
+    plan[3] = B;
+    plan[4] = Hv;
+    plan[5] = plan[6] = plan[7] = 0;
+  }
+  __syncthreads();  // prefix[] (global) written by this CTA is visible to it after the barrier
+  int4* cta = reinterpret_cast<int4*>(plan + kPlanHeaderWords);
+  for (int c = tid; c < grid; c += 256) {
+    const long long x = (long long)c * tpc;
+    int4 e = make_int4(-1, 0, 0, 0);
+    if (x < total) {
+      // largest s with Hv * prefix[s] <= x  (prefix is non-decreasing; empty sequences repeat a value,
+      // taking the largest index lands on the sequence that owns x)
+      int lo = 0, hi = B;  // invariant: Hv*prefix[lo] <= x < Hv*prefix[hi]
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((long long)prefix[mid] * Hv <= x) lo = mid; else hi = mid;
+      }
+      const int s = lo;
+      const int nt = prefix[s + 1] - prefix[s];
+      const long long r = x - (long long)prefix[s] * Hv;
+      e.x = s;
+      e.y = (int)(r / nt);
+      e.z = (int)(r % nt);
+      const long long left = total - x;
+      e.w = (int)(left < tpc ? left : tpc);
+    }
+    cta[c] = e;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// merge: one CTA per (sequence, virtual kv head) pair; G x D outputs.
+// ------------------------------------------------------------------------------------------------
+struct MergeParams {
+  const int32_t* plan;
+  const float* ws_o;
+  const float* ws_ml;
+  void* out;
+  int64_t out_stride_t, out_stride_h;
+  const float* v_scale;
+  float* lse_out;
+  int scale_stride;
+  int Hq, G, gsplit, D;
+};
+
+template <int ODT>
+__global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
+  extern __shared__ float wts[];  // [G][n_parts] normalised weights
+  __shared__ float lse_s[kMaxGroup];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int32_t* plan = p.plan;
+  const int total = plan[0], tpc = plan[1], Hv = plan[4];
+  if (total <= 0) return;
+  const int pair = blockIdx.x;
+  const int s = pair / Hv, hv = pair - s * Hv;
+  const int32_t* prefix = plan + kPlanPrefixOffset;
+  const int nt = prefix[s + 1] - prefix[s];
+  if (nt == 0) return;
+  const long long x0 = (long long)prefix[s] * Hv + (long long)hv * nt;
+  const long long x1 = x0 + nt;
+  const int c_lo = (int)(x0 / tpc), c_hi = (int)((x1 - 1) / tpc);
+  if (c_lo == c_hi) return;  // whole pair lived in one CTA: decode already wrote the final output
+  const int np = c_hi - c_lo + 1;
+  const int slot_lo = (x0 == (long long)c_lo * tpc) ? 0 : 1;  // later CTAs start on this pair: slot 0
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+  // pass 1: per head, global max / sum over the partials with warp shuffles; weights to smem
+  for (int head = wid; head < p.G; head += 4) {
+    float mg = -INFINITY;
+    for (int i = lane; i < np; i += 32) {
+      const size_t pidx = ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head;
+      mg = fmaxf(mg, p.ws_ml[pidx * 2]);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
+    float lg = 0.f;
+    for (int i = lane; i < np; i += 32) {
+      const size_t pidx = ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head;
+      const float wgt = fast_exp2(p.ws_ml[pidx * 2] - mg);
+      wts[head * np + i] = wgt;
+      lg += p.ws_ml[pidx * 2 + 1] * wgt;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
+    const float inv = 1.0f / lg;
+    for (int i = lane; i < np; i += 32) wts[head * np + i] *= inv;
+    if (lane == 0) lse_s[head] = (mg + fast_log2(lg)) * 0.6931471805599453f;
+  }
+  __syncthreads();
+
+  // pass 2: weighted sum of the partial outputs; consecutive threads -> consecutive head dims
+  const int kvh = hv / p.gsplit;
+  const float vscale = p.v_scale ? p.v_scale[(int64_t)kvh * p.scale_stride] : 1.0f;
+  using E = Elem<ODT>;
+  for (int idx = tid; idx < p.G * p.D; idx += 128) {
+    const int head = idx / p.D, d = idx - head * p.D;
+    float acc = 0.f;
+    const float* wh = wts + head * np;
+#pragma unroll 4
+    for (int i = 0; i < np; ++i) {
+      const size_t pidx = ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head;
+      acc += wh[i] * __ldg(p.ws_o + pidx * p.D + d);
+    }
+    const int hq = hv * p.G + head;
+    typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+    op[d] = E::from_float(acc * vscale);
+    if (d == 0 && p.lse_out) p.lse_out[(int64_t)s * p.Hq + hq] = lse_s[head];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// LSE merge of P full attention results (sequence-split exchange across shards / ranks).
+// One warp per (row, head); lanes stride the head dim.
+// ------------------------------------------------------------------------------------------------
+template <int DT>
+__global__ void __launch_bounds__(128) merge_lse_kernel(const void* parts_o, const float* parts_lse, int P,
+                                                        int64_t stride_o, int64_t stride_lse, void* out, float* lse_out,
+                                                        int64_t rows /* n * Hq */, int D) {
+  pdl_wait();
+  pdl_launch_dependents();
+  using E = Elem<DT>;
+  const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float mx = -INFINITY;
+  for (int i = 0; i < P; ++i) mx = fmaxf(mx, parts_lse[i * stride_lse + row]);
+  float den = 0.f;
+  for (int i = 0; i < P; ++i) {
+    const float l = parts_lse[i * stride_lse + row];
+    den += (l == -INFINITY) ? 0.f : __expf(l - mx);
+  }
+  const typename E::type* po = reinterpret_cast<const typename E::type*>(parts_o);
+  typename E::type* oo = reinterpret_cast<typename E::type*>(out);
+  for (int d = lane; d < D; d += 32) {
+    float acc = 0.f;
+    for (int i = 0; i < P; ++i) {
+      const float l = parts_lse[i * stride_lse + row];
+      const float wgt = (l == -INFINITY) ? 0.f : __expf(l - mx);
+      acc += wgt * E::to_float(po[i * stride_o + row * D + d]);
+    }
+    oo[row * D + d] = E::from_float(den > 0.f ? acc / den : 0.f);
+  }
+  if (lane == 0 && lse_out) lse_out[row] = den > 0.f ? mx + __logf(den) : -INFINITY;
+}
+
+int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
+
+static int split_group(int Hq, int Hkv, int* G, int* gsplit) {
+  if (Hkv <= 0 || Hq <= 0 || Hq % Hkv) return -1;
+  const int Gfull = Hq / Hkv;
+  int gs = 1;
+  while (gs <= Gfull && (Gfull / gs > kMaxGroup || (Gfull % gs) != 0)) ++gs;
+  if (gs > Gfull) return -1;
+  *G = Gfull / gs;
+  *gsplit = gs;
+  return 0;
+}
+
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" size_t b200attn_plan_bytes(int32_t max_num_seqs) {
+  if (max_num_seqs < 0) max_num_seqs = 0;
+  return ((size_t)kPlanPrefixOffset + (size_t)max_num_seqs + 1 + 3) / 4 * 4 * sizeof(int32_t);
+}
+
+extern "C" size_t b200attn_workspace_bytes(int32_t head_dim, int32_t num_ctas) {
+  if (num_ctas <= 0 || num_ctas > kMaxGrid) num_ctas = kMaxGrid;
+  return (ws_o_floats(num_ctas, head_dim) + ws_ml_floats(num_ctas)) * sizeof(float);
+}
+
+extern "C" int b200attn_decode_plan(const int32_t* seq_lens, int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads,
+                                    int32_t num_ctas, void* plan, size_t plan_bytes, void* stream) {
+  if (!seq_lens || !plan) {
+    set_error("decode_plan: null pointer argument");
+    return B200ATTN_EINVAL;
+  }
+  int G, gsplit;
+  if (num_seqs < 0 || split_group(num_q_heads, num_kv_heads, &G, &gsplit)) {
+    set_error("decode_plan: bad shape B=%d Hq=%d Hkv=%d", num_seqs, num_q_heads, num_kv_heads);
+    return B200ATTN_EINVAL;
+  }
+  if (num_ctas <= 0 || num_ctas > kMaxGrid) {
+    set_error("decode_plan: num_ctas %d out of range (1..%d)", num_ctas, kMaxGrid);
+    return B200ATTN_EINVAL;
+  }
+  if (plan_bytes < b200attn_plan_bytes(num_seqs)) {
+    set_error("decode_plan: plan buffer too small (%zu < %zu)", plan_bytes, b200attn_plan_bytes(num_seqs));
+    return B200ATTN_ENOSPACE;
+  }
+  int B = num_seqs, Hv = num_kv_heads * gsplit, grid = num_ctas;
+  int32_t* pl = reinterpret_cast<int32_t*>(plan);
+  void* args[] = {(void*)&seq_lens, &B, &Hv, &grid, &pl};
+  return launch_with_pdl((const void*)plan_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(stream), args);
+}
+
+extern "C" int b200attn_merge(const void* plan, int32_t num_ctas, const void* workspace, void* out, int64_t out_stride_t,
+                              int64_t out_stride_h, int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads,
+                              int32_t head_dim, int32_t out_dtype, const float* v_scale, int32_t scale_stride,
+                              float* lse_out, void* stream) {
+  if (num_seqs == 0) return B200ATTN_OK;
+  if (!plan || !workspace || !out) {
+    set_error("merge: null pointer argument");
+    return B200ATTN_EINVAL;
+  }
+  int G, gsplit;
+  if (split_group(num_q_heads, num_kv_heads, &G, &gsplit)) {
+    set_error("merge: bad head counts Hq=%d Hkv=%d", num_q_heads, num_kv_heads);
+    return B200ATTN_EINVAL;
+  }
+  if (num_ctas <= 0 || num_ctas > kMaxGrid) {
+    set_error("merge: num_ctas %d out of range", num_ctas);
+    return B200ATTN_EINVAL;
+  }
+  if (out_dtype != B200ATTN_BF16 && out_dtype != B200ATTN_FP16) {
+    set_error("merge: out dtype must be bf16 or fp16");
+    return B200ATTN_EINVAL;
+  }
+  MergeParams p;
+  p.plan = reinterpret_cast<const int32_t*>(plan);
+  p.ws_o = reinterpret_cast<const float*>(workspace);
+  p.ws_ml = p.ws_o + ws_o_floats(num_ctas, head_dim);
+  p.out = out; p.out_stride_t = out_stride_t; p.out_stride_h = out_stride_h;
+  p.v_scale = v_scale; p.scale_stride = scale_stride; p.lse_out = lse_out;
+  p.Hq = num_q_heads; p.G = G; p.gsplit = gsplit; p.D = head_dim;
+  const int Hv = num_kv_heads * gsplit;
+  const size_t smem = (size_t)G * num_ctas * sizeof(float);  // a pair spans at most num_ctas partials
+  const void* fn = out_dtype == B200ATTN_BF16 ? (const void*)merge_kernel<B200ATTN_BF16> : (const void*)merge_kernel<B200ATTN_FP16>;
+  if (smem > 48 * 1024) {
+    if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute(merge smem)"))
+      return B200ATTN_ECUDA;
+  }
+  void* args[] = {&p};
+  return launch_with_pdl(fn, dim3((unsigned)(num_seqs * Hv)), dim3(128), smem, static_cast<cudaStream_t>(stream), args);
+}
+
+extern "C" int b200attn_merge_lse(const void* parts_o, const float* parts_lse, int32_t num_parts, int64_t part_stride_o,
+                                  int64_t part_stride_lse, void* out, float* lse_out, int32_t n, int32_t num_q_heads,
+                                  int32_t head_dim, int32_t dtype, void* stream) {
+  if (n == 0) return B200ATTN_OK;
+  if (!parts_o || !parts_lse || !out || num_parts <= 0) {
+    set_error("merge_lse: null pointer or no parts");
+    return B200ATTN_EINVAL;
+  }
+  if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) {
+    set_error("merge_lse: dtype must be bf16 or fp16");
+    return B200ATTN_EINVAL;
+  }
+  int64_t rows = (int64_t)n * num_q_heads;
+  int P = num_parts, D = head_dim;
+  const void* fn = dtype == B200ATTN_BF16 ? (const void*)merge_lse_kernel<B200ATTN_BF16> : (const void*)merge_lse_kernel<B200ATTN_FP16>;
+  void* args[] = {(void*)&parts_o, (void*)&parts_lse, &P, &part_stride_o, &part_stride_lse, &out, &lse_out, &rows, &D};
+  return launch_with_pdl(fn, dim3((unsigned)((rows + 3) / 4)), dim3(128), 0, static_cast<cudaStream_t>(stream), args);
+}

@@ -1,0 +1,202 @@
+"""torch.library custom ops over the C ABI: ``torch.ops.b200attn.{kv_write, decode_plan, paged_decode, merge_lse}``.
+
+They are what ``backend.B200PagedAttentionImpl`` calls from ``do_kv_cache_update`` / ``forward`` — the same two
+call sites the reference reaches through ``torch.ops.vllm.unified_kv_cache_update`` and
+``unified_attention_with_output`` ($VLLM/model_executor/layers/attention/attention.py:691-761).  Registered as
+custom ops (with fake impls) so they trace under torch.compile and capture into CUDA graphs like the ops they
+replace.  PyTorch only supplies device memory and the current stream here; all arithmetic is in libb200attn.
+
+Tensor conventions (same as vLLM's): key/value/query ``[T, H, D]``; ``k_cache``/``v_cache`` are the two planes of
+the paged cache viewed as ``[num_blocks, block_size, Hkv, D]`` with ANY strides (HND physical layout preferred);
+``slot_mapping`` int64 ``[T]`` (-1 = padding); ``block_table`` int32 ``[B, max_blocks]``; ``seq_lens`` int32 ``[B]``;
+``k_scale``/``v_scale`` fp32 with 1 element (per-tensor) or Hkv elements (per-head).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import DT_BF16, DT_FP16, DT_FP8_E4M3, B200AttnError, check, load_library
+
+_FP8_DTYPES = (torch.uint8, torch.float8_e4m3fn)
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return DT_BF16
+    if t.dtype == torch.float16:
+        return DT_FP16
+    if t.dtype in _FP8_DTYPES:
+        return DT_FP8_E4M3
+    raise B200AttnError(f"unsupported dtype {t.dtype}")
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _require_cuda(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise B200AttnError("b200attn ops need CUDA tensors: there is no CPU fallback for this path")
+
+
+def _scale_stride(scale: torch.Tensor, num_kv_heads: int) -> int:
+    n = scale.numel()
+    if n == 1:
+        return 0
+    if n == num_kv_heads and scale.is_contiguous():
+        return 1
+    raise B200AttnError(f"kv scale must have 1 or Hkv={num_kv_heads} contiguous elements, got shape {tuple(scale.shape)}")
+
+
+def _cache_strides(k_cache: torch.Tensor, v_cache: torch.Tensor):
+    if k_cache.dim() != 4 or v_cache.shape != k_cache.shape or v_cache.stride() != k_cache.stride():
+        raise B200AttnError("k_cache / v_cache must be [num_blocks, block_size, Hkv, D] views with identical strides")
+    if k_cache.stride(3) != 1:
+        raise B200AttnError("cache head_dim must be contiguous")
+    return k_cache.stride(0), k_cache.stride(1), k_cache.stride(2)
+
+
+def default_ctas(kv_dtype: torch.dtype) -> int:
+    """Persistent decode grid for this device: 2 CTAs/SM (fp8 KV) or 1 CTA/SM (16-bit KV)."""
+    n = load_library().b200attn_default_ctas(DT_FP8_E4M3 if kv_dtype in _FP8_DTYPES else DT_BF16)
+    if n <= 0:
+        raise B200AttnError("no CUDA device: libb200attn has no CPU fallback")
+    return n
+
+
+def plan_numel(max_num_seqs: int) -> int:
+    return load_library().b200attn_plan_bytes(max_num_seqs) // 4
+
+
+def workspace_numel(head_dim: int, num_ctas: int) -> int:
+    return load_library().b200attn_workspace_bytes(head_dim, num_ctas) // 4
+
+
+# ------------------------------------------------------------------------------------------------
+# kv_write
+# ------------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200attn::kv_write", mutates_args=("k_cache", "v_cache"), device_types="cuda")
+def kv_write(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+             slot_mapping: torch.Tensor, k_scale: torch.Tensor, v_scale: torch.Tensor) -> None:
+    _require_cuda(key, value, k_cache, v_cache, slot_mapping)
+    lib = load_library()
+    T = slot_mapping.shape[0]
+    if T == 0:
+        return
+    if key.dim() != 3 or value.shape != key.shape or key.stride(2) != 1 or value.stride(2) != 1:
+        raise B200AttnError("key/value must be [T, Hkv, D] with contiguous head_dim")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous():
+        raise B200AttnError("slot_mapping must be contiguous int64")
+    Hkv, D = key.shape[1], key.shape[2]
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    kvdt = _dt(k_cache)
+    sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
+    check(lib.b200attn_kv_write(
+        key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1), value.stride(0), value.stride(1),
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, slot_mapping.data_ptr(), T, Hkv, D, k_cache.shape[1],
+        _dt(key), kvdt, k_scale.data_ptr(), v_scale.data_ptr(), sstride, _stream(key)), "b200attn_kv_write")
+
+
+@kv_write.register_fake
+def _(key, value, k_cache, v_cache, slot_mapping, k_scale, v_scale) -> None:
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+# decode_plan (once per step) and paged_decode (= split-KV decode kernel + merge kernel)
+# ------------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200attn::decode_plan", mutates_args=("plan",), device_types="cuda")
+def decode_plan(seq_lens: torch.Tensor, plan: torch.Tensor, num_q_heads: int, num_kv_heads: int, num_ctas: int) -> None:
+    _require_cuda(seq_lens, plan)
+    if seq_lens.dtype != torch.int32 or plan.dtype != torch.int32 or not seq_lens.is_contiguous():
+        raise B200AttnError("seq_lens and plan must be contiguous int32")
+    check(load_library().b200attn_decode_plan(seq_lens.data_ptr(), seq_lens.shape[0], num_q_heads, num_kv_heads, num_ctas,
+                                              plan.data_ptr(), plan.numel() * 4, _stream(plan)), "b200attn_decode_plan")
+
+
+@decode_plan.register_fake
+def _(seq_lens, plan, num_q_heads, num_kv_heads, num_ctas) -> None:
+    return None
+
+
+@torch.library.custom_op("b200attn::paged_decode", mutates_args=("out", "workspace", "lse"), device_types="cuda")
+def paged_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
+                 seq_lens: torch.Tensor, out: torch.Tensor, plan: torch.Tensor, workspace: torch.Tensor,
+                 k_scale: torch.Tensor, v_scale: torch.Tensor, sm_scale: float, num_ctas: int,
+                 lse: torch.Tensor | None = None) -> None:
+    _require_cuda(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace)
+    lib = load_library()
+    B = seq_lens.shape[0]
+    if B == 0:
+        return
+    if query.dim() != 3 or out.dim() != 3 or query.stride(2) != 1 or out.stride(2) != 1 or query.dtype != out.dtype:
+        raise B200AttnError("query/out must be [B, Hq, D] of the same dtype with contiguous head_dim")
+    if block_table.dtype != torch.int32 or seq_lens.dtype != torch.int32 or block_table.stride(1) != 1:
+        raise B200AttnError("block_table / seq_lens must be int32 (block_table rows contiguous)")
+    Hq, D = query.shape[1], query.shape[2]
+    nb, bs, Hkv = k_cache.shape[0], k_cache.shape[1], k_cache.shape[2]
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    kvdt = _dt(k_cache)
+    sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
+    lse_ptr = lse.data_ptr() if lse is not None else None
+    st = _stream(query)
+    check(lib.b200attn_decode(
+        query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1),
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, nb, block_table.data_ptr(), block_table.stride(0),
+        seq_lens.data_ptr(), B, Hq, Hkv, D, bs, _dt(query), kvdt, float(sm_scale), k_scale.data_ptr(),
+        v_scale.data_ptr(), sstride, plan.data_ptr(), num_ctas, workspace.data_ptr(), workspace.numel() * 4, lse_ptr, st),
+        "b200attn_decode")
+    check(lib.b200attn_merge(
+        plan.data_ptr(), num_ctas, workspace.data_ptr(), out.data_ptr(), out.stride(0), out.stride(1), B, Hq, Hkv, D,
+        _dt(out), v_scale.data_ptr() if kvdt == DT_FP8_E4M3 else None, sstride, lse_ptr, st), "b200attn_merge")
+
+
+@paged_decode.register_fake
+def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale, num_ctas, lse=None) -> None:
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+# merge_lse: combine P attention results by log-sum-exp (sequence-split across shards / ranks)
+# ------------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200attn::merge_lse", mutates_args=("out", "lse_out"), device_types="cuda")
+def merge_lse(parts_o: torch.Tensor, parts_lse: torch.Tensor, out: torch.Tensor, lse_out: torch.Tensor | None = None) -> None:
+    """parts_o [P, n, Hq, D] (bf16/fp16), parts_lse [P, n, Hq] fp32 natural log; out [n, Hq, D]."""
+    _require_cuda(parts_o, parts_lse, out)
+    if not (parts_o.is_contiguous() and parts_lse.is_contiguous() and out.is_contiguous()):
+        raise B200AttnError("merge_lse needs contiguous tensors")
+    P, n, Hq, D = parts_o.shape
+    check(load_library().b200attn_merge_lse(
+        parts_o.data_ptr(), parts_lse.data_ptr(), P, parts_o.stride(0), parts_lse.stride(0), out.data_ptr(),
+        lse_out.data_ptr() if lse_out is not None else None, n, Hq, D, _dt(out), _stream(out)), "b200attn_merge_lse")
+
+
+@merge_lse.register_fake
+def _(parts_o, parts_lse, out, lse_out=None) -> None:
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+# Convenience wrapper owning the plan / workspace buffers (what the metadata builder keeps per device)
+# ------------------------------------------------------------------------------------------------
+class DecodeWorkspace:
+    """Pre-allocated, capture-safe buffers for one device: plan (int32) + split-KV partials (fp32)."""
+
+    def __init__(self, device, max_num_seqs: int, kv_dtype: torch.dtype, head_dim: int = 128, num_ctas: int | None = None):
+        self.device = torch.device(device)
+        with torch.cuda.device(self.device):
+            self.num_ctas = int(num_ctas) if num_ctas else default_ctas(kv_dtype)
+        self.max_num_seqs = max_num_seqs
+        self.plan = torch.zeros(plan_numel(max_num_seqs), dtype=torch.int32, device=self.device)
+        self.workspace = torch.empty(workspace_numel(head_dim, self.num_ctas), dtype=torch.float32, device=self.device)
+
+    def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int) -> None:
+        if seq_lens.shape[0] > self.max_num_seqs:
+            raise B200AttnError(f"batch {seq_lens.shape[0]} exceeds planned max_num_seqs {self.max_num_seqs}")
+        torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.num_ctas)
+
+    def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None) -> None:
+        torch.ops.b200attn.paged_decode(query, k_cache, v_cache, block_table, seq_lens, out, self.plan, self.workspace,
+                                        k_scale, v_scale, sm_scale, self.num_ctas, lse)

@@ -1,0 +1,167 @@
+/*
+ * b200attn.h — C ABI of libb200attn.so: the sm_100a paged-decode attention hot path.
+ *
+ * This is the drop-in boundary for the AR-stage hot path of ht-vllm-omni.
+ * The reference has no native code of its own for this path: it calls vLLM's compiled ops
+ * from `AttentionImpl.do_kv_cache_update` / `AttentionImpl.forward`.  Each entry point below
+ * names the reference-side call it replaces.  `$VLLM` = vllm 0.22.0 site-packages (the
+ * un-vendored dependency the reference delegates the arithmetic to; reference pins
+ * vllm==0.18.0 in docs/getting_started/quickstart.md:22).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every data pointer is a DEVICE pointer unless it says host;
+ *   - strides are in ELEMENTS of the pointed-to dtype;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - stateless and capture-safe: no allocation, no host sync, no device->host copy inside;
+ *   - return 0 on success, a negative B200ATTN_E* code otherwise; b200attn_last_error() then
+ *     returns a thread-local, human-readable host string.  Nothing throws.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     B200ATTN_ECUDA.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define B200ATTN_API __attribute__((visibility("default")))
+#else
+#define B200ATTN_API
+#endif
+
+/* element types */
+#define B200ATTN_BF16 0
+#define B200ATTN_FP16 1
+#define B200ATTN_FP8_E4M3 2 /* KV cache only; 1 byte per element */
+
+/* error codes */
+#define B200ATTN_OK 0
+#define B200ATTN_EINVAL (-1)  /* bad argument / unsupported shape */
+#define B200ATTN_ECUDA (-2)   /* CUDA runtime / driver error (incl. no device) */
+#define B200ATTN_ENOSPACE (-3) /* plan or workspace buffer too small */
+
+/* geometry constants the host side needs */
+#define B200ATTN_TILE_TOKENS 64 /* scheduling granule of the split-KV decode kernel */
+#define B200ATTN_MAX_GROUP 16   /* query heads sharing one KV head handled per CTA */
+
+B200ATTN_API int b200attn_abi_version(void);
+B200ATTN_API const char* b200attn_last_error(void);
+
+/* Number of SMs of the current device (0 if none); decode grids are sized from it. */
+B200ATTN_API int b200attn_sm_count(void);
+
+/*
+ * Kernel 1 — KV write + in-register FP8 quantisation ("reshape_and_cache").
+ * Replaces: torch.ops._C_cache_ops.reshape_and_cache_flash as called from
+ *   $VLLM/v1/attention/backends/flashinfer.py:1828-1855 (FlashInferImpl.do_kv_cache_update) and
+ *   $VLLM/v1/attention/backends/triton_attn.py:720-763 (spec: ops/triton_reshape_and_cache_flash.py:17-124),
+ *   reached from vllm_omni/worker/gpu_ar_model_runner.py:228-298 via unified_kv_cache_update.
+ *
+ * For every token t with slot = slot_mapping[t] >= 0:
+ *   cache[slot / block_size][slot % block_size][h][:] = cvt(key[t][h][:] / k_scale[h*scale_stride])
+ * fp8: fp32 IEEE division then round-to-nearest-even, saturate-to-finite e4m3; 16-bit: bit copy.
+ * k_cache / v_cache are the base pointers of the K and V planes; both use the same
+ * (stride_block, stride_slot, stride_head) and a unit stride along D.
+ */
+B200ATTN_API int b200attn_kv_write(const void* key, const void* value,
+                      int64_t key_stride_t, int64_t key_stride_h,
+                      int64_t value_stride_t, int64_t value_stride_h,
+                      void* k_cache, void* v_cache,
+                      int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                      const int64_t* slot_mapping, int32_t num_tokens,
+                      int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                      int32_t in_dtype, int32_t kv_dtype,
+                      const float* k_scale, const float* v_scale, int32_t scale_stride,
+                      void* stream);
+
+/*
+ * Split-KV work plan (once per decode step, shared by all layers).
+ * Replaces: the per-step planning in AttentionMetadataBuilder.build
+ *   ($VLLM/v1/attention/backends/flashinfer.py:886-1248 `plan`, triton_attn.py:216-268).
+ *
+ * Cuts the flat list of (sequence, kv head, 64-token tile) work items into equal contiguous
+ * ranges, one per persistent CTA, entirely on the device (no host sync, capture-safe).
+ * `plan` must hold b200attn_plan_bytes(num_seqs) bytes.  `num_ctas` is the decode grid: use
+ * b200attn_default_ctas(kv_dtype) (2 CTAs/SM for fp8, 1 for 16-bit KV); tests pass small values
+ * to force many split points.  The SAME num_ctas must be given to decode and merge.
+ */
+B200ATTN_API size_t b200attn_plan_bytes(int32_t max_num_seqs);
+B200ATTN_API int b200attn_default_ctas(int32_t kv_dtype);
+B200ATTN_API int b200attn_decode_plan(const int32_t* seq_lens, int32_t num_seqs,
+                         int32_t num_q_heads, int32_t num_kv_heads,
+                         int32_t num_ctas, void* plan, size_t plan_bytes, void* stream);
+
+/* Bytes of split-KV workspace (partial o, m, l) the decode + merge kernels need. */
+B200ATTN_API size_t b200attn_workspace_bytes(int32_t head_dim, int32_t num_ctas);
+
+/*
+ * Kernel 2 — split-KV paged flash-decoding.
+ * Replaces: the decode branch of AttentionImpl.forward, i.e.
+ *   flashinfer.decode.trtllm_batch_decode_with_kv_cache ($VLLM/v1/attention/backends/flashinfer.py:1751-1822)
+ *   and kernel_unified_attention ($VLLM/v1/attention/ops/triton_unified_attention.py:178-643).
+ *
+ * out[b][hq][:] = softmax(sm_scale * k_scale * q[b][hq] . K[b][hq/G]^T) . V[b][hq/G] * v_scale over the
+ * first seq_lens[b] tokens addressed through block_table[b][*].  Sequences whose whole range falls
+ * inside one CTA are written to `out` directly; the others leave (o, m, l) partials in `workspace`
+ * for b200attn_merge.  q/out dtype = q_dtype; kv_dtype fp8 accepts either q dtype, 16-bit KV must
+ * equal q_dtype.  head_dim must be 128; block_size a multiple of 16.
+ * The K/V planes are read through TMA: base pointers and byte strides must be 16-byte aligned.
+ */
+B200ATTN_API int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+                    void* out, int64_t out_stride_t, int64_t out_stride_h,
+                    const void* k_cache, const void* v_cache,
+                    int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                    int64_t num_blocks,
+                    const int32_t* block_table, int64_t block_table_stride,
+                    const int32_t* seq_lens, int32_t num_seqs,
+                    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                    int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
+                    float sm_scale, const float* k_scale, const float* v_scale,
+                    int32_t scale_stride,
+                    const void* plan, int32_t num_ctas,
+                    void* workspace, size_t workspace_bytes,
+                    float* lse_out /* nullable, [num_seqs][num_q_heads] natural-log LSE */,
+                    void* stream);
+
+/*
+ * Kernel 3 — merge of split-KV partials (online-softmax reduction with warp shuffles).
+ * Replaces: reduce_segments ($VLLM/v1/attention/ops/triton_unified_attention.py:645-733) and the
+ *   in-kernel reduction of the TRT-LLM-gen "MultiCtasKv" cubins.
+ * Must follow b200attn_decode on the same stream with the same plan / num_ctas / workspace / out.
+ */
+B200ATTN_API int b200attn_merge(const void* plan, int32_t num_ctas, const void* workspace,
+                   void* out, int64_t out_stride_t, int64_t out_stride_h,
+                   int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                   int32_t out_dtype, const float* v_scale, int32_t scale_stride,
+                   float* lse_out, void* stream);
+
+/*
+ * Cross-rank / cross-shard merge by log-sum-exp (sequence-split "DCP" exchange):
+ *   out = sum_p o_p * exp(lse_p - lse) / sum_p exp(lse_p - lse).
+ * Replaces: _C.merge_attn_states ($VLLM/v1/attention/ops/merge_attn_states.py:7-101) and
+ *   cp_lse_ag_out_rs ($VLLM/v1/attention/backends/flashinfer.py:1714-1738), generalised to P parts.
+ * parts_o: [P][n][Hq][D] (dtype), parts_lse: [P][n][Hq] fp32 (natural log).  -inf LSE = empty part.
+ */
+B200ATTN_API int b200attn_merge_lse(const void* parts_o, const float* parts_lse, int32_t num_parts,
+                       int64_t part_stride_o, int64_t part_stride_lse,
+                       void* out, float* lse_out, int32_t n, int32_t num_q_heads,
+                       int32_t head_dim, int32_t dtype, void* stream);
+
+/*
+ * Runtime knobs (host, process-wide): "pdl" (programmatic dependent launch, default 1),
+ * "force_simt" (route every group size to the CUDA-core consumer, default 0).
+ * Returns the previous value or B200ATTN_EINVAL for an unknown name.
+ */
+B200ATTN_API int b200attn_set_option(const char* name, int32_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */
