@@ -143,7 +143,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     uint32_t stage = 0, phase = 0, sg = 0;
     const uint16_t* qptr = reinterpret_cast<const uint16_t*>(p.q);
     while (remaining > 0) {
-      const int L = __ldg(p.seq_lens + s);
+      const int L = max(__ldg(p.seq_lens + s), 0);
       const int nt = (L + kTileTokens - 1) / kTileTokens;
       const int n = min(remaining, nt - tile);
       // ---- query rows of this segment + its descriptor ----
