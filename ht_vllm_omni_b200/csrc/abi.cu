@@ -13,6 +13,8 @@ namespace b200attn {
 static thread_local char g_err[512] = "";
 static int g_opt_pdl = 1;
 static int g_opt_force_simt = 0;
+static int g_opt_debug = 0;
+static unsigned long long* g_dbg_buf = nullptr;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -29,6 +31,8 @@ int check_cuda(cudaError_t e, const char* what) {
 }
 
 int option_force_simt() { return g_opt_force_simt; }
+int option_debug() { return g_opt_debug; }
+unsigned long long* option_debug_buffer() { return g_dbg_buf; }
 
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args) {
   cudaLaunchConfig_t cfg;
@@ -127,6 +131,7 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
   int* slot = nullptr;
   if (!strcmp(name, "pdl")) slot = &g_opt_pdl;
   else if (!strcmp(name, "force_simt")) slot = &g_opt_force_simt;
+  else if (!strcmp(name, "debug")) slot = &g_opt_debug;
   if (!slot) {
     set_error("set_option: unknown option '%s'", name);
     return B200ATTN_EINVAL;
@@ -134,4 +139,9 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
   const int prev = *slot;
   *slot = value;
   return prev;
+}
+
+// debug only: device buffer of [num_ctas][8] uint64 that the decode kernel fills with %globaltimer stamps
+extern "C" __attribute__((visibility("default"))) void b200attn_debug_set_timeline_buffer(void* dev_ptr) {
+  g_dbg_buf = reinterpret_cast<unsigned long long*>(dev_ptr);
 }

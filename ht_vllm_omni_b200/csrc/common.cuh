@@ -119,6 +119,13 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t& r0, u
                : "r"(addr));
 }
 
+// transpose an 8x8 matrix of b16 held one row-pair per thread: in: thread (g,t) = M[g][2t,2t+1]; out: M[2t,2t+1][g]
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
+  uint32_t d;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
+}
+
 // two e4m3 bytes (low / high half of a 32-bit word) -> packed f16x2 (exact)
 __device__ __forceinline__ uint32_t e4m3x2_to_f16x2_lo(uint32_t w) {
   uint32_t r;

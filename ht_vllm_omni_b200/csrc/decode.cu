@@ -44,6 +44,8 @@ struct DecodeParams {
   int G;                // query heads per virtual kv head (<= 16)
   int gsplit;           // virtual heads per physical kv head
   int cpb;              // 16-token chunks per cache block (block_size / 16)
+  unsigned long long* dbg;  // debug timeline buffer [grid][8] (globaltimer ns) or nullptr
+  int debug;            // bit0: consumers skip the math (pure streaming ceiling); never set in production
 };
 
 constexpr int kD = 128;
@@ -74,6 +76,14 @@ struct Smem {
   static constexpr int kTotalBytes = kStages * kStageBytes + kFixedBytes + 1024;  // +1024: manual alignment
   static_assert(kStages >= 3, "pipeline too shallow");
 };
+
+__device__ __forceinline__ void dbg_stamp(const DecodeParams& p, int slot) {
+  if (p.dbg != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.dbg[(size_t)blockIdx.x * 8 + slot] = t;
+  }
+}
 
 template <int QDT>
 __device__ __forceinline__ float q_to_float(uint16_t raw) {
@@ -112,6 +122,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -135,6 +146,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
 
   const int4 cs = __ldg(reinterpret_cast<const int4*>(p.plan + kPlanHeaderWords) + blockIdx.x);
   if (cs.x < 0 || cs.w <= 0) return;  // idle CTA (fewer tiles than CTAs)
+  if (threadIdx.x == 0) dbg_stamp(p, 1);
 
   if (warp == kConsumerWarps) {
     // =========================================== producer ===========================================
@@ -189,6 +201,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
             tma_load_4d(dst + 2048, tm, full_bar(stage), 64, row0, kvh, b, pol);
           }
         }
+        if (sg == 0 && tt == 0 && lane == 0) dbg_stamp(p, 2);
         if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
       remaining -= n;
@@ -207,6 +220,12 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   }
 
   // ============================================= consumers =============================================
+  // MMA roles (mma.sync m16n8k16, fp32 accumulate):
+  //   S^T(16 tok x 8 heads) = K(16 tok x d) . Q^T(d x 8 heads)     A = K rows straight from the swizzled tile
+  //   O^T(16 d x 8 heads)  += V^T(16 d x 16 tok) . P^T(16 tok x 8 heads)
+  // so the GQA group sits on the N side (8 or 2x8 heads, no padding rows) and a thread owns the softmax statistics
+  // of exactly the heads (2t, 2t+1) whose O^T columns it accumulates.  P^T goes from the S^T accumulator layout to the
+  // B-operand layout with two movmatrix.trans per 8 heads.
   const int w = warp;
   const int g = lane >> 2;
   const int t = lane & 3;
@@ -214,6 +233,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   int remaining = cs.w;
   uint32_t stage = 0, phase = 0, sg = 0;
   const float ninf = -INFINITY;
+  constexpr float kLazy = 8.0f;  // rescale O only when a row maximum grows by more than 2^8 (P <= 256 fits f16/bf16)
 
   while (remaining > 0) {
     const uint32_t slot = sg & 1;
@@ -225,83 +245,82 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     const int L = desc[slot * 8 + 4];
     const int kvh = hv / p.gsplit;
 
-    // ---- Q fragments (A operand: rows = heads g / g+8, k = permuted head-dim) ----
-    uint32_t qa[8][4];
-    float crow_lo, crow_hi;
+    // ---- Q fragments (B operand: n = head g (+8), k = permuted head-dim) ----
+    uint32_t qb[NT][8][2];
+    float crow[NT][2];  // logit scale (log2 domain) of heads 8a+2t and 8a+2t+1
     {
       const float kscale = kFp8 ? __ldg(p.k_scale + (int64_t)kvh * p.scale_stride) : 1.0f;
       const uint32_t qs = q_base + slot * kQSlotBytes;
-      const bool lo_ok = g < p.G;
-      const bool hi_ok = (NT == 2) && (g + 8 < p.G);
-      uint2 rlo[8], rhi[8];
 #pragma unroll
-      for (int st = 0; st < 8; ++st) {
-        const int dbase = kFp8 ? (32 * t + 4 * st) : (64 * (st >> 2) + 16 * t + 4 * (st & 3));
-        rlo[st] = lo_ok ? lds64(qs + g * (kD * 2) + dbase * 2) : make_uint2(0u, 0u);
-        rhi[st] = hi_ok ? lds64(qs + (g + 8) * (kD * 2) + dbase * 2) : make_uint2(0u, 0u);
+      for (int a = 0; a < NT; ++a) {
+        const int head = a * 8 + g;
+        const bool ok = head < p.G;
+        uint2 r[8];
+#pragma unroll
+        for (int st = 0; st < 8; ++st) {
+          const int dbase = kFp8 ? (32 * t + 4 * st) : (64 * (st >> 2) + 16 * t + 4 * (st & 3));
+          r[st] = ok ? lds64(qs + head * (kD * 2) + dbase * 2) : make_uint2(0u, 0u);
+        }
+        float f = 1.0f;  // factor folded back into the logit scale
+        if constexpr (kFp8 && QDT == B200ATTN_BF16) {
+          // bf16 -> f16 with an exact per-head power-of-two pre-scale (keeps any finite bf16 row inside f16 range)
+          float amax = 0.f;
+#pragma unroll
+          for (int st = 0; st < 8; ++st)
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(q_to_float<QDT>(r[st].x & 0xffff)), fabsf(q_to_float<QDT>(r[st].x >> 16))),
+                                     fmaxf(fabsf(q_to_float<QDT>(r[st].y & 0xffff)), fabsf(q_to_float<QDT>(r[st].y >> 16)))));
+          amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+          amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+          const uint32_t eb = (__float_as_uint(amax) >> 23) & 0xffu;
+          // inv = 2^(8-e) puts the row maximum in [256, 512); f = 2^(e-8) undoes it on the logits.  Rows whose maximum
+          // is below 2^-111 (biased exponent < 16) are left alone: their logits are ~0 either way.
+          const float inv = eb >= 16 ? __uint_as_float((262u - eb) << 23) : 1.0f;
+          f = eb >= 16 ? __uint_as_float((eb - 8u) << 23) : 1.0f;
+#pragma unroll
+          for (int st = 0; st < 8; ++st) {
+            qb[a][st][0] = pack_f32x2<false>(q_to_float<QDT>(r[st].x & 0xffff) * inv, q_to_float<QDT>(r[st].x >> 16) * inv);
+            qb[a][st][1] = pack_f32x2<false>(q_to_float<QDT>(r[st].y & 0xffff) * inv, q_to_float<QDT>(r[st].y >> 16) * inv);
+          }
+        } else {
+#pragma unroll
+          for (int st = 0; st < 8; ++st) { qb[a][st][0] = r[st].x; qb[a][st][1] = r[st].y; }
+        }
+        // the statistics / accumulators of heads (2t, 2t+1) live in this thread: fetch their factors from lanes g = head
+        const float c = f * p.sm_scale_log2 * kscale;
+        crow[a][0] = __shfl_sync(0xffffffffu, c, (2 * t) << 2);
+        crow[a][1] = __shfl_sync(0xffffffffu, c, (2 * t + 1) << 2);
       }
-      float f_lo = 1.0f, f_hi = 1.0f;  // factor folded back into the logit scale
-      if constexpr (kFp8 && QDT == B200ATTN_BF16) {
-        // bf16 -> f16 with an exact per-row power-of-two pre-scale (keeps any finite bf16 row in f16 range)
-        float amax_lo = 0.f, amax_hi = 0.f;
-#pragma unroll
-        for (int st = 0; st < 8; ++st) {
-          amax_lo = fmaxf(amax_lo, fmaxf(fmaxf(fabsf(q_to_float<QDT>(rlo[st].x & 0xffff)), fabsf(q_to_float<QDT>(rlo[st].x >> 16))),
-                                         fmaxf(fabsf(q_to_float<QDT>(rlo[st].y & 0xffff)), fabsf(q_to_float<QDT>(rlo[st].y >> 16)))));
-          amax_hi = fmaxf(amax_hi, fmaxf(fmaxf(fabsf(q_to_float<QDT>(rhi[st].x & 0xffff)), fabsf(q_to_float<QDT>(rhi[st].x >> 16))),
-                                         fmaxf(fabsf(q_to_float<QDT>(rhi[st].y & 0xffff)), fabsf(q_to_float<QDT>(rhi[st].y >> 16)))));
-        }
-        amax_lo = fmaxf(amax_lo, __shfl_xor_sync(0xffffffffu, amax_lo, 1));
-        amax_lo = fmaxf(amax_lo, __shfl_xor_sync(0xffffffffu, amax_lo, 2));
-        amax_hi = fmaxf(amax_hi, __shfl_xor_sync(0xffffffffu, amax_hi, 1));
-        amax_hi = fmaxf(amax_hi, __shfl_xor_sync(0xffffffffu, amax_hi, 2));
-        const uint32_t eb_lo = (__float_as_uint(amax_lo) >> 23) & 0xffu;
-        const uint32_t eb_hi = (__float_as_uint(amax_hi) >> 23) & 0xffu;
-        // inv = 2^(8-e) puts the row maximum in [256, 512); f = 2^(e-8) undoes it on the logits.  Rows whose
-        // maximum is below 2^-111 (biased exponent < 16) are left alone: their logits are ~0 either way.
-        const float inv_lo = eb_lo >= 16 ? __uint_as_float((262u - eb_lo) << 23) : 1.0f;
-        const float inv_hi = eb_hi >= 16 ? __uint_as_float((262u - eb_hi) << 23) : 1.0f;
-        f_lo = eb_lo >= 16 ? __uint_as_float((eb_lo - 8u) << 23) : 1.0f;
-        f_hi = eb_hi >= 16 ? __uint_as_float((eb_hi - 8u) << 23) : 1.0f;
-#pragma unroll
-        for (int st = 0; st < 8; ++st) {
-          qa[st][0] = pack_f32x2<false>(q_to_float<QDT>(rlo[st].x & 0xffff) * inv_lo, q_to_float<QDT>(rlo[st].x >> 16) * inv_lo);
-          qa[st][2] = pack_f32x2<false>(q_to_float<QDT>(rlo[st].y & 0xffff) * inv_lo, q_to_float<QDT>(rlo[st].y >> 16) * inv_lo);
-          qa[st][1] = pack_f32x2<false>(q_to_float<QDT>(rhi[st].x & 0xffff) * inv_hi, q_to_float<QDT>(rhi[st].x >> 16) * inv_hi);
-          qa[st][3] = pack_f32x2<false>(q_to_float<QDT>(rhi[st].y & 0xffff) * inv_hi, q_to_float<QDT>(rhi[st].y >> 16) * inv_hi);
-        }
-      } else {
-#pragma unroll
-        for (int st = 0; st < 8; ++st) {
-          qa[st][0] = rlo[st].x; qa[st][2] = rlo[st].y;
-          qa[st][1] = rhi[st].x; qa[st][3] = rhi[st].y;
-        }
-      }
-      crow_lo = f_lo * p.sm_scale_log2 * kscale;
-      crow_hi = f_hi * p.sm_scale_log2 * kscale;
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(qempty_bar(slot));
 
-    float m_lo = ninf, m_hi = ninf, l_lo = 0.f, l_hi = 0.f;
+    float m_run[NT][2], l_run[NT][2];
     float o[NT][8][4];
 #pragma unroll
-    for (int a = 0; a < NT; ++a)
+    for (int a = 0; a < NT; ++a) {
+      m_run[a][0] = m_run[a][1] = ninf;
+      l_run[a][0] = l_run[a][1] = 0.f;
 #pragma unroll
       for (int b = 0; b < 8; ++b)
 #pragma unroll
         for (int c = 0; c < 4; ++c) o[a][b][c] = 0.f;
+    }
 
     for (int tt = 0; tt < n; ++tt) {
       mbar_wait(full_bar(stage), phase);
+      if (sg == 0 && tt == 0 && tid == 0) dbg_stamp(p, 3);
       const int tok0 = (tile0 + tt) * kTileTokens + w * kChunkTokens;
-      if (tok0 < L) {
+      if (tok0 < L && !(p.debug & 1)) {
         const uint32_t kbase = stages_base + stage * kStageBytes + w * kChunkBytes;
         const uint32_t vbase = kbase + kConsumerWarps * kChunkBytes;
         const bool partial = tok0 + kChunkTokens > L;
 
-        // ---------------- S = Q.K^T : two 8-token n-tiles (sA: tokens 0-7, sB: tokens 8-15) ----------------
-        float sA[4] = {0.f, 0.f, 0.f, 0.f}, sB[4] = {0.f, 0.f, 0.f, 0.f};
+        // ---------------- S^T = K.Q^T : two accumulator chains (even / odd k-steps) per 8 heads ----------------
+        float sa[NT][4], sb[NT][4];
+#pragma unroll
+        for (int a = 0; a < NT; ++a)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) sa[a][c] = sb[a][c] = 0.f;
         if constexpr (kFp8) {
           const uint32_t rA = kbase + g * 128, rB = kbase + (g + 8) * 128;
           const uint32_t c0 = (uint32_t)((2 * t) ^ g) << 4, c1 = (uint32_t)((2 * t + 1) ^ g) << 4;
@@ -311,8 +330,13 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
           const uint32_t kbw[8] = {kb0.x, kb0.y, kb0.z, kb0.w, kb1.x, kb1.y, kb1.z, kb1.w};
 #pragma unroll
           for (int st = 0; st < 8; ++st) {
-            mma_16816<false>(sA, qa[st][0], qa[st][1], qa[st][2], qa[st][3], e4m3x2_to_f16x2_lo(kaw[st]), e4m3x2_to_f16x2_hi(kaw[st]));
-            mma_16816<false>(sB, qa[st][0], qa[st][1], qa[st][2], qa[st][3], e4m3x2_to_f16x2_lo(kbw[st]), e4m3x2_to_f16x2_hi(kbw[st]));
+            const uint32_t a0 = e4m3x2_to_f16x2_lo(kaw[st]), a2 = e4m3x2_to_f16x2_hi(kaw[st]);
+            const uint32_t a1 = e4m3x2_to_f16x2_lo(kbw[st]), a3 = e4m3x2_to_f16x2_hi(kbw[st]);
+#pragma unroll
+            for (int a = 0; a < NT; ++a) {
+              if (st & 1) mma_16816<false>(sb[a], a0, a1, a2, a3, qb[a][st][0], qb[a][st][1]);
+              else mma_16816<false>(sa[a], a0, a1, a2, a3, qb[a][st][0], qb[a][st][1]);
+            }
           }
         } else {
 #pragma unroll
@@ -323,76 +347,50 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
               const uint4 ka = lds128(kbase + hf * 2048 + g * 128 + co);
               const uint4 kb = lds128(kbase + hf * 2048 + (g + 8) * 128 + co);
               const int st = hf * 4 + i * 2;
-              mma_16816<kMmaBf16>(sA, qa[st][0], qa[st][1], qa[st][2], qa[st][3], ka.x, ka.y);
-              mma_16816<kMmaBf16>(sA, qa[st + 1][0], qa[st + 1][1], qa[st + 1][2], qa[st + 1][3], ka.z, ka.w);
-              mma_16816<kMmaBf16>(sB, qa[st][0], qa[st][1], qa[st][2], qa[st][3], kb.x, kb.y);
-              mma_16816<kMmaBf16>(sB, qa[st + 1][0], qa[st + 1][1], qa[st + 1][2], qa[st + 1][3], kb.z, kb.w);
+#pragma unroll
+              for (int a = 0; a < NT; ++a) {
+                mma_16816<kMmaBf16>(sa[a], ka.x, kb.x, ka.y, kb.y, qb[a][st][0], qb[a][st][1]);
+                mma_16816<kMmaBf16>(sb[a], ka.z, kb.z, ka.w, kb.w, qb[a][st + 1][0], qb[a][st + 1][1]);
+              }
             }
           }
         }
 
-        // ---------------- online softmax (log2 domain) ----------------
-        // thread (g,t) holds S[head g][tok 2t,2t+1] in s?[0..1] and S[head g+8][..] in s?[2..3]
-        float x[8];
-        x[0] = sA[0] * crow_lo; x[1] = sA[1] * crow_lo; x[2] = sB[0] * crow_lo; x[3] = sB[1] * crow_lo;
-        x[4] = sA[2] * crow_hi; x[5] = sA[3] * crow_hi; x[6] = sB[2] * crow_hi; x[7] = sB[3] * crow_hi;
-        if (partial) {
-          const int j0 = tok0 + 2 * t;
-          if (j0 >= L) { x[0] = ninf; x[4] = ninf; }
-          if (j0 + 1 >= L) { x[1] = ninf; x[5] = ninf; }
-          if (j0 + 8 >= L) { x[2] = ninf; x[6] = ninf; }
-          if (j0 + 9 >= L) { x[3] = ninf; x[7] = ninf; }
-        }
-        float mx_lo = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
-        mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 1));
-        mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 2));
-        float mx_hi = ninf;
-        if constexpr (NT == 2) {
-          mx_hi = fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7]));
-          mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 1));
-          mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 2));
-        }
-        const bool grow = (mx_lo > m_lo) || (NT == 2 && mx_hi > m_hi);
-        if (__any_sync(0xffffffffu, grow)) {
-          const float mn_lo = fmaxf(m_lo, mx_lo);
-          const float al_lo = fast_exp2(m_lo - mn_lo);  // m_lo = -inf -> 0
-          l_lo *= al_lo;
-          m_lo = mn_lo;
-          // O^T accumulators carry heads along t: fetch alpha of heads 2t and 2t+1
-          const float a0 = __shfl_sync(0xffffffffu, al_lo, (2 * t) << 2);
-          const float a1 = __shfl_sync(0xffffffffu, al_lo, (2 * t + 1) << 2);
+        // ---------------- online softmax (log2 domain, lazy rescale) ----------------
+        // thread (g,t): x[a][0] = S[head 8a+2t][tok g], [1] = S[head 8a+2t+1][tok g], [2]/[3] = same heads, tok g+8
+        uint32_t pb[NT][2];
 #pragma unroll
-          for (int mt = 0; mt < 8; ++mt) {
-            o[0][mt][0] *= a0; o[0][mt][1] *= a1; o[0][mt][2] *= a0; o[0][mt][3] *= a1;
+        for (int a = 0; a < NT; ++a) {
+          float x0 = (sa[a][0] + sb[a][0]) * crow[a][0], x1 = (sa[a][1] + sb[a][1]) * crow[a][1];
+          float x2 = (sa[a][2] + sb[a][2]) * crow[a][0], x3 = (sa[a][3] + sb[a][3]) * crow[a][1];
+          if (partial) {
+            if (tok0 + g >= L) { x0 = ninf; x1 = ninf; }
+            if (tok0 + g + 8 >= L) { x2 = ninf; x3 = ninf; }
           }
-          if constexpr (NT == 2) {
-            const float mn_hi = fmaxf(m_hi, mx_hi);
-            const float al_hi = fast_exp2(m_hi - mn_hi);
-            l_hi *= al_hi;
-            m_hi = mn_hi;
-            const float b0 = __shfl_sync(0xffffffffu, al_hi, (2 * t) << 2);
-            const float b1 = __shfl_sync(0xffffffffu, al_hi, (2 * t + 1) << 2);
+          float mx0 = fmaxf(x0, x2), mx1 = fmaxf(x1, x3);
+#pragma unroll
+          for (int off = 4; off < 32; off <<= 1) {
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, off));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, off));
+          }
+          const bool need = (mx0 > m_run[a][0] + kLazy) || (mx1 > m_run[a][1] + kLazy);  // -inf + 8 = -inf: first chunk
+          if (__any_sync(0xffffffffu, need)) {
+            const float n0 = fmaxf(m_run[a][0], mx0), n1 = fmaxf(m_run[a][1], mx1);
+            const float al0 = fast_exp2(m_run[a][0] - n0), al1 = fast_exp2(m_run[a][1] - n1);  // (-inf) - finite -> 0
+            m_run[a][0] = n0; m_run[a][1] = n1;
+            l_run[a][0] *= al0; l_run[a][1] *= al1;
 #pragma unroll
             for (int mt = 0; mt < 8; ++mt) {
-              o[1][mt][0] *= b0; o[1][mt][1] *= b1; o[1][mt][2] *= b0; o[1][mt][3] *= b1;
+              o[a][mt][0] *= al0; o[a][mt][1] *= al1; o[a][mt][2] *= al0; o[a][mt][3] *= al1;
             }
           }
-        }
-        uint32_t pb[NT][2];
-        {
-          const float p0 = fast_exp2(x[0] - m_lo), p1 = fast_exp2(x[1] - m_lo);
-          const float p2 = fast_exp2(x[2] - m_lo), p3 = fast_exp2(x[3] - m_lo);
-          l_lo += (p0 + p1) + (p2 + p3);
-          pb[0][0] = pack_f32x2<kMmaBf16>(p0, p1);
-          pb[0][1] = pack_f32x2<kMmaBf16>(p2, p3);
-          if constexpr (NT == 2) {
-            // rows g+8 >= G hold zero queries: their m/l/o are never stored, exp2(0 - 0) = 1 is harmless
-            const float q0 = fast_exp2(x[4] - m_hi), q1 = fast_exp2(x[5] - m_hi);
-            const float q2 = fast_exp2(x[6] - m_hi), q3 = fast_exp2(x[7] - m_hi);
-            l_hi += (q0 + q1) + (q2 + q3);
-            pb[1][0] = pack_f32x2<kMmaBf16>(q0, q1);
-            pb[1][1] = pack_f32x2<kMmaBf16>(q2, q3);
-          }
+          const float p0 = fast_exp2(x0 - m_run[a][0]), p1 = fast_exp2(x1 - m_run[a][1]);
+          const float p2 = fast_exp2(x2 - m_run[a][0]), p3 = fast_exp2(x3 - m_run[a][1]);
+          l_run[a][0] += p0 + p2;
+          l_run[a][1] += p1 + p3;
+          // [tok g][heads 2t,2t+1] --movmatrix.trans--> [head g][toks 2t,2t+1] = B fragment of P^T
+          pb[a][0] = movmatrix_trans(pack_f32x2<kMmaBf16>(p0, p1));
+          pb[a][1] = movmatrix_trans(pack_f32x2<kMmaBf16>(p2, p3));
         }
 
         // ---------------- O^T(d x heads) += V^T(d x tok) . P^T(tok x heads) ----------------
@@ -422,8 +420,8 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
               const uint32_t x23 = __byte_perm(w2[r], w3[r], sel);
               const uint32_t a0 = e4m3x2_to_f16x2_lo(x01), a1 = e4m3x2_to_f16x2_hi(x01);
               const uint32_t a2 = e4m3x2_to_f16x2_lo(x23), a3 = e4m3x2_to_f16x2_hi(x23);
-              mma_16816<false>(o[0][2 * r + hb], a0, a1, a2, a3, pb[0][0], pb[0][1]);
-              if constexpr (NT == 2) mma_16816<false>(o[1][2 * r + hb], a0, a1, a2, a3, pb[1][0], pb[1][1]);
+#pragma unroll
+              for (int a = 0; a < NT; ++a) mma_16816<false>(o[a][2 * r + hb], a0, a1, a2, a3, pb[a][0], pb[a][1]);
             }
           }
         } else {
@@ -442,8 +440,8 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
             uint32_t a0, a1, a2, a3;
             ldmatrix_x4_trans(addr, a0, a1, a2, a3);
             a0 &= keep_lo; a1 &= keep_lo; a2 &= keep_hi; a3 &= keep_hi;
-            mma_16816<kMmaBf16>(o[0][mt], a0, a1, a2, a3, pb[0][0], pb[0][1]);
-            if constexpr (NT == 2) mma_16816<kMmaBf16>(o[1][mt], a0, a1, a2, a3, pb[1][0], pb[1][1]);
+#pragma unroll
+            for (int a = 0; a < NT; ++a) mma_16816<kMmaBf16>(o[a][mt], a0, a1, a2, a3, pb[a][0], pb[a][1]);
           }
         }
       }
@@ -452,19 +450,19 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
       if (++stage == kStages) { stage = 0; phase ^= 1; }
     }
 
+    if (tid == 0 && remaining == n) dbg_stamp(p, 4);
     // ---------------- segment end: combine the 4 warps' (m, l, O) ----------------
-    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 1);
-    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 2);
-    if constexpr (NT == 2) {
-      l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 1);
-      l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 2);
-    }
-    if (t == 0) {
-      red_ml[(w * kMaxGroup + g) * 2 + 0] = m_lo;
-      red_ml[(w * kMaxGroup + g) * 2 + 1] = l_lo;
-      if constexpr (NT == 2) {
-        red_ml[(w * kMaxGroup + g + 8) * 2 + 0] = m_hi;
-        red_ml[(w * kMaxGroup + g + 8) * 2 + 1] = l_hi;
+#pragma unroll
+    for (int a = 0; a < NT; ++a) {
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        float l = l_run[a][hh];
+#pragma unroll
+        for (int off = 4; off < 32; off <<= 1) l += __shfl_xor_sync(0xffffffffu, l, off);
+        if (g == 0) {
+          red_ml[(w * kMaxGroup + a * 8 + 2 * t + hh) * 2 + 0] = m_run[a][hh];
+          red_ml[(w * kMaxGroup + a * 8 + 2 * t + hh) * 2 + 1] = l;
+        }
       }
     }
     named_bar_sync(1, kConsumerWarps * 32);
@@ -526,6 +524,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     remaining -= n;
     ++sg;
   }
+  if (tid == 0) dbg_stamp(p, 5);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -535,6 +534,8 @@ int encode_kv_tensor_map(CUtensorMap* tm, const void* base, int kv_dtype, int64_
                          int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D);
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
 int option_force_simt();
+int option_debug();
+unsigned long long* option_debug_buffer();
 
 template <int KVT, int QDT, int NT>
 static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, cudaStream_t stream) {
@@ -643,6 +644,8 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stri
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.B = num_seqs; p.Hq = num_q_heads; p.Hv = num_kv_heads * gsplit; p.G = G; p.gsplit = gsplit;
   p.cpb = block_size / kChunkTokens;
+  p.debug = option_debug();
+  p.dbg = option_debug_buffer();
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nt = G > 8 ? 2 : 1;

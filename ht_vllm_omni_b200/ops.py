@@ -121,40 +121,58 @@ def _(seq_lens, plan, num_q_heads, num_kv_heads, num_ctas) -> None:
     return None
 
 
-@torch.library.custom_op("b200attn::paged_decode", mutates_args=("out", "workspace", "lse"), device_types="cuda")
-def paged_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
-                 seq_lens: torch.Tensor, out: torch.Tensor, plan: torch.Tensor, workspace: torch.Tensor,
-                 k_scale: torch.Tensor, v_scale: torch.Tensor, sm_scale: float, num_ctas: int,
-                 lse: torch.Tensor | None = None) -> None:
-    _require_cuda(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace)
-    lib = load_library()
-    B = seq_lens.shape[0]
-    if B == 0:
-        return
+def _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale):
     if query.dim() != 3 or out.dim() != 3 or query.stride(2) != 1 or out.stride(2) != 1 or query.dtype != out.dtype:
         raise B200AttnError("query/out must be [B, Hq, D] of the same dtype with contiguous head_dim")
     if block_table.dtype != torch.int32 or seq_lens.dtype != torch.int32 or block_table.stride(1) != 1:
         raise B200AttnError("block_table / seq_lens must be int32 (block_table rows contiguous)")
-    Hq, D = query.shape[1], query.shape[2]
-    nb, bs, Hkv = k_cache.shape[0], k_cache.shape[1], k_cache.shape[2]
-    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    Hkv = k_cache.shape[2]
     kvdt = _dt(k_cache)
-    sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
-    lse_ptr = lse.data_ptr() if lse is not None else None
-    st = _stream(query)
-    check(lib.b200attn_decode(
+    return _cache_strides(k_cache, v_cache), kvdt, (_scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0)
+
+
+def launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
+                        num_ctas, lse=None) -> None:
+    """Kernel 2 only (b200attn_decode): final rows for unsplit sequences, (o, m, l) partials for the rest."""
+    (sb, ss, sh), kvdt, sstride = _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale)
+    check(load_library().b200attn_decode(
         query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1),
-        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, nb, block_table.data_ptr(), block_table.stride(0),
-        seq_lens.data_ptr(), B, Hq, Hkv, D, bs, _dt(query), kvdt, float(sm_scale), k_scale.data_ptr(),
-        v_scale.data_ptr(), sstride, plan.data_ptr(), num_ctas, workspace.data_ptr(), workspace.numel() * 4, lse_ptr, st),
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, k_cache.shape[0], block_table.data_ptr(), block_table.stride(0),
+        seq_lens.data_ptr(), seq_lens.shape[0], query.shape[1], k_cache.shape[2], query.shape[2], k_cache.shape[1],
+        _dt(query), kvdt, float(sm_scale), k_scale.data_ptr(), v_scale.data_ptr(), sstride, plan.data_ptr(), num_ctas,
+        workspace.data_ptr(), workspace.numel() * 4, lse.data_ptr() if lse is not None else None, _stream(query)),
         "b200attn_decode")
-    check(lib.b200attn_merge(
-        plan.data_ptr(), num_ctas, workspace.data_ptr(), out.data_ptr(), out.stride(0), out.stride(1), B, Hq, Hkv, D,
-        _dt(out), v_scale.data_ptr() if kvdt == DT_FP8_E4M3 else None, sstride, lse_ptr, st), "b200attn_merge")
+
+
+def launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse=None) -> None:
+    """Kernel 3 only (b200attn_merge); must follow launch_split_decode on the same stream."""
+    kvdt = _dt(k_cache)
+    Hkv = k_cache.shape[2]
+    sstride = _scale_stride(v_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
+    check(load_library().b200attn_merge(
+        plan.data_ptr(), num_ctas, workspace.data_ptr(), out.data_ptr(), out.stride(0), out.stride(1), seq_lens.shape[0],
+        out.shape[1], Hkv, out.shape[2], _dt(out), v_scale.data_ptr() if kvdt == DT_FP8_E4M3 else None, sstride,
+        lse.data_ptr() if lse is not None else None, _stream(out)), "b200attn_merge")
+
+
+@torch.library.custom_op("b200attn::paged_decode", mutates_args=("out", "workspace", "lse"), device_types="cuda")
+def paged_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
+                 seq_lens: torch.Tensor, out: torch.Tensor, plan: torch.Tensor, workspace: torch.Tensor,
+                 k_scale: torch.Tensor, v_scale: torch.Tensor, sm_scale: float, num_ctas: int,
+                 lse: torch.Tensor) -> None:
+    """`lse`: fp32 [B, Hq] to receive the natural-log LSE, or an EMPTY tensor to skip it (a required argument:
+    optional mutable tensors trip torch.library's version-counter bump when omitted)."""
+    _require_cuda(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace)
+    if seq_lens.shape[0] == 0:
+        return
+    lse = lse if lse.numel() > 0 else None
+    launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
+                        num_ctas, lse)
+    launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse)
 
 
 @paged_decode.register_fake
-def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale, num_ctas, lse=None) -> None:
+def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale, num_ctas, lse) -> None:
     return None
 
 
@@ -162,9 +180,10 @@ def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_sc
 # merge_lse: combine P attention results by log-sum-exp (sequence-split across shards / ranks)
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("b200attn::merge_lse", mutates_args=("out", "lse_out"), device_types="cuda")
-def merge_lse(parts_o: torch.Tensor, parts_lse: torch.Tensor, out: torch.Tensor, lse_out: torch.Tensor | None = None) -> None:
-    """parts_o [P, n, Hq, D] (bf16/fp16), parts_lse [P, n, Hq] fp32 natural log; out [n, Hq, D]."""
+def merge_lse(parts_o: torch.Tensor, parts_lse: torch.Tensor, out: torch.Tensor, lse_out: torch.Tensor) -> None:
+    """parts_o [P, n, Hq, D] (bf16/fp16), parts_lse [P, n, Hq] fp32 natural log; out [n, Hq, D]; lse_out [n, Hq] or empty."""
     _require_cuda(parts_o, parts_lse, out)
+    lse_out = lse_out if lse_out.numel() > 0 else None
     if not (parts_o.is_contiguous() and parts_lse.is_contiguous() and out.is_contiguous()):
         raise B200AttnError("merge_lse needs contiguous tensors")
     P, n, Hq, D = parts_o.shape
@@ -174,7 +193,7 @@ def merge_lse(parts_o: torch.Tensor, parts_lse: torch.Tensor, out: torch.Tensor,
 
 
 @merge_lse.register_fake
-def _(parts_o, parts_lse, out, lse_out=None) -> None:
+def _(parts_o, parts_lse, out, lse_out) -> None:
     return None
 
 
@@ -191,6 +210,7 @@ class DecodeWorkspace:
         self.max_num_seqs = max_num_seqs
         self.plan = torch.zeros(plan_numel(max_num_seqs), dtype=torch.int32, device=self.device)
         self.workspace = torch.empty(workspace_numel(head_dim, self.num_ctas), dtype=torch.float32, device=self.device)
+        self._no_lse = torch.empty(0, dtype=torch.float32, device=self.device)
 
     def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int) -> None:
         if seq_lens.shape[0] > self.max_num_seqs:
@@ -199,4 +219,4 @@ class DecodeWorkspace:
 
     def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None) -> None:
         torch.ops.b200attn.paged_decode(query, k_cache, v_cache, block_table, seq_lens, out, self.plan, self.workspace,
-                                        k_scale, v_scale, sm_scale, self.num_ctas, lse)
+                                        k_scale, v_scale, sm_scale, self.num_ctas, self._no_lse if lse is None else lse)

@@ -175,5 +175,46 @@ def check_16bit():
     assert np.array_equal(O, P @ V), "16-bit PV map wrong"
 
 
+def check_swapped_qk_and_movmatrix():
+    """Round-1b layout: S^T(16 tok x 8 heads) = K.Q^T with K as the A operand, then movmatrix.trans to the P^T B operand."""
+    Q = rng.integers(-4, 5, size=(8, D)).astype(float)       # 8 heads
+    K = rng.integers(-4, 5, size=(16, D)).astype(float)
+    kph = swizzle_store(K)
+    ST = np.zeros((16, 8))
+    for st in range(8):
+        Af, Bf = [], []
+        for lane in range(32):
+            g, t = lane >> 2, lane & 3
+            dbase = 32 * t + 4 * st
+            i, r = st >> 2, st & 3
+            chunk = 2 * t + i
+            wg = kph[g * 128 + ((chunk ^ g) << 4) + 4 * r:][:4]
+            wg8 = kph[(g + 8) * 128 + ((chunk ^ g) << 4) + 4 * r:][:4]
+            # a0 = lo(word row g), a1 = lo(word row g+8), a2 = hi(row g), a3 = hi(row g+8)
+            Af.append([(wg[0], wg[1]), (wg8[0], wg8[1]), (wg[2], wg[3]), (wg8[2], wg8[3])])
+            Bf.append([(Q[g, dbase], Q[g, dbase + 1]), (Q[g, dbase + 2], Q[g, dbase + 3])])
+        ST += mma(Af, Bf)
+    assert np.array_equal(ST, K @ Q.T), "swapped QK map wrong"
+    # C fragment -> packed pairs -> movmatrix.trans -> B fragment of P^T (k = token, n = head)
+    P = ST  # treat logits as probabilities for the layout check: P^T[tok][head]
+    r0 = {}; r1 = {}
+    for lane in range(32):
+        g, t = lane >> 2, lane & 3
+        c = c_frag(P, lane)          # c0,c1 = [tok g][head 2t,2t+1]; c2,c3 = [tok g+8][...]
+        r0[lane] = (c[0], c[1]); r1[lane] = (c[2], c[3])
+    def movm(regs):
+        M = np.zeros((8, 8))
+        for lane in range(32):
+            g, t = lane >> 2, lane & 3
+            M[g, 2 * t], M[g, 2 * t + 1] = regs[lane]
+        return {lane: (M[2 * (lane & 3), lane >> 2], M[2 * (lane & 3) + 1, lane >> 2]) for lane in range(32)}
+    b0, b1 = movm(r0), movm(r1)
+    for lane in range(32):
+        g, t = lane >> 2, lane & 3
+        assert b0[lane] == (P[2 * t, g], P[2 * t + 1, g])          # {B[k=2t][n=g], B[k=2t+1][n=g]}, B[k][n] = P^T[tok k][head n]
+        assert b1[lane] == (P[2 * t + 8, g], P[2 * t + 9, g])
+
+
 if __name__ == "__main__":
+    check_swapped_qk_and_movmatrix()
     check_fp8(); check_16bit(); print("fragment maps OK")
