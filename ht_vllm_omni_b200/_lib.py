@@ -13,6 +13,8 @@ DT_BF16, DT_FP16, DT_FP8_E4M3 = 0, 1, 2
 TILE_TOKENS = 64
 MAX_GROUP = 16
 MAX_CTAS = 1024
+ABI_VERSION = 2
+DECODE_FUSED_MERGE = 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
@@ -41,7 +43,7 @@ PROTOTYPES = {
     "b200attn_decode_plan": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _sz, _p]),
     "b200attn_workspace_bytes": (_sz, [_i32, _i32]),
     "b200attn_decode": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _p, _i32,
-                                  _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32, _p, _sz, _p, _p]),
+                                  _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32, _p, _sz, _p, _p, _i32, _i32, _p]),
     "b200attn_merge": (C.c_int, [_p, _i32, _p, _p, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p]),
     "b200attn_merge_lse": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
     "b200attn_set_option": (C.c_int, [C.c_char_p, _i32]),
@@ -67,7 +69,7 @@ def load_library():
             fn = getattr(lib, name)  # AttributeError here = header / library drift
             fn.restype = res
             fn.argtypes = args
-        if lib.b200attn_abi_version() != 1:
+        if lib.b200attn_abi_version() != ABI_VERSION:
             raise B200AttnError("libb200attn ABI version mismatch")
         _LIB = lib
         return lib

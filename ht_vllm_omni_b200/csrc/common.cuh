@@ -26,10 +26,14 @@ static_assert(kTileTokens == B200ATTN_TILE_TOKENS, "header / kernel tile mismatc
 // Plan buffer layout (int32 words):
 //   [0] total_tiles  [1] tiles_per_cta  [2] grid  [3] num_seqs  [4] num_kv_heads (virtual)  [5..7] 0
 //   [8 .. 8+kMaxGrid*4)         int4 cta_start[kMaxGrid] = {seq, kv_head, tile, n_tiles}  (seq=-1: idle)
-//   [8+kMaxGrid*4 .. +B+1)      tile_prefix[num_seqs+1] (exclusive scan of ceil(L/64))
+//   [.. +kMaxGrid*2)            arrival counters of the in-kernel merge, one per (first CTA, slot) of a split
+//                               (sequence, kv head) pair; zeroed by the plan kernel, self-resetting afterwards
+//   [.. +B+1)                   tile_prefix[num_seqs+1] (exclusive scan of ceil(L/64))
 constexpr int kPlanHeaderWords = 8;
 constexpr int kPlanCtaWords = kMaxGrid * 4;
-constexpr int kPlanPrefixOffset = kPlanHeaderWords + kPlanCtaWords;
+constexpr int kPlanCounterOffset = kPlanHeaderWords + kPlanCtaWords;
+constexpr int kPlanCounterWords = kMaxGrid * 2;
+constexpr int kPlanPrefixOffset = kPlanCounterOffset + kPlanCounterWords;
 
 // Workspace layout: ws_o [grid][2 slots][16 heads][D] fp32, then ws_ml [grid][2][16][2] fp32.
 __host__ __device__ inline size_t ws_o_floats(int grid, int D) { return (size_t)grid * 2 * kMaxGroup * D; }
@@ -106,6 +110,17 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+// L2-coherent loads that the compiler must not reorder or merge (the in-kernel merge issues them in a chosen order)
+__device__ __forceinline__ float ldcg_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float2 ldcg_f32x2(const float* p) {
+  float2 v;
+  asm volatile("ld.global.cg.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {

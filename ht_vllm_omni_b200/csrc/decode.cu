@@ -32,7 +32,8 @@ struct DecodeParams {
   const int32_t* block_table;
   int64_t bt_stride;
   const int32_t* seq_lens;
-  const int32_t* plan;
+  const int32_t* row_map;  // nullable: block-table row of decode row s (query-token rows of one request share a row)
+  int32_t* plan;           // read-only except the arrival counters of the in-kernel merge
   float* ws_o;
   float* ws_ml;
   const float* k_scale;
@@ -44,10 +45,15 @@ struct DecodeParams {
   int G;                // query heads per virtual kv head (<= 16)
   int gsplit;           // virtual heads per physical kv head
   int cpb;              // 16-token chunks per cache block (block_size / 16)
+  int fresh;            // trailing positions of a row the preceding kernel may have written (< 0: unknown, no early prefetch)
+  int fused_merge;      // 1: the last CTA to finish a split (sequence, kv head) pair merges its partials in-kernel
   unsigned long long* dbg;  // debug timeline buffer [grid][8] (globaltimer ns) or nullptr
   int debug;            // bit0: consumers skip the math (pure streaming ceiling); never set in production
 };
 
+#ifndef B200_FP8_CTAS_NT1
+#define B200_FP8_CTAS_NT1 2
+#endif
 constexpr int kD = 128;
 constexpr int kQSlotBytes = kMaxGroup * kD * 2;  // 4 KiB: 16 query rows
 constexpr int kRedStride = kD + 4;               // floats; +4 keeps rows 16-byte aligned and staggers banks
@@ -65,16 +71,17 @@ struct Smem {
   static constexpr int kStageBytes = KvCfg<KVT>::kStageBytes;
   static constexpr int kRedOBytes = kConsumerWarps * NT * 8 * kRedStride * 4;
   static constexpr int kRedMlBytes = kConsumerWarps * kMaxGroup * 2 * 4;
-  static constexpr int kDescBytes = 2 * 32;
+  static constexpr int kDescBytes = 3 * 32;   // 2 segment descriptors + merge hand-off words
   static constexpr int kBarBytes = 256;
   static constexpr int kFixedBytes = 2 * kQSlotBytes + kRedOBytes + kRedMlBytes + kDescBytes + kBarBytes;
-  // fp8: 2 CTAs / SM (113 KiB each); 16-bit: 1 CTA / SM (227 KiB)
-  static constexpr int kCtas = KvCfg<KVT>::kFp8 ? 2 : 1;
-  static constexpr int kBudget = kCtas == 2 ? 113 * 1024 : 227 * 1024;
+  // fp8: 3 CTAs / SM (75 KiB each) for G <= 8, 2 CTAs / SM (113 KiB) for G <= 16; 16-bit: 1 CTA / SM (227 KiB)
+  static constexpr int kCtas = KvCfg<KVT>::kFp8 ? (NT == 1 ? B200_FP8_CTAS_NT1 : 2) : 1;
+  static constexpr int kBudget = kCtas == 3 ? 75 * 1024 : (kCtas == 2 ? 113 * 1024 : 227 * 1024);
   static constexpr int kStagesRaw = (kBudget - kFixedBytes - 1024) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTotalBytes = kStages * kStageBytes + kFixedBytes + 1024;  // +1024: manual alignment
   static_assert(kStages >= 3, "pipeline too shallow");
+  static_assert(kTotalBytes <= kBudget, "smem budget exceeded");
 };
 
 __device__ __forceinline__ void dbg_stamp(const DecodeParams& p, int slot) {
@@ -139,9 +146,11 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   }
   __syncthreads();
 
-  // Everything above overlaps the tail of the preceding kernel (KV write / plan); from here on we read
-  // memory it produced.
-  pdl_wait();
+  // Programmatic dependent launch: let the kernel after us (the next layer's KV write) get resident early, then run the
+  // part of our prologue that does not depend on the preceding kernel.  What may be touched BEFORE griddepcontrol.wait:
+  // the plan, seq_lens and block_table (step-level metadata, older than the preceding kernel) and K/V tiles that lie
+  // entirely below L - fresh (`fresh` = trailing positions the preceding kernel may have written; < 0 = unknown).
+  // Q, the newest tokens, `out`, the workspace and the merge counters are only touched after the wait.
   pdl_launch_dependents();
 
   const int4 cs = __ldg(reinterpret_cast<const int4*>(p.plan + kPlanHeaderWords) + blockIdx.x);
@@ -154,28 +163,43 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     int s = cs.x, hv = cs.y, tile = cs.z, remaining = cs.w;
     uint32_t stage = 0, phase = 0, sg = 0;
     const uint16_t* qptr = reinterpret_cast<const uint16_t*>(p.q);
+    bool waited = false;
+    int early_left = p.fresh >= 0 ? kStages : 0;  // tiles we may still issue before the wait (ring is empty at start)
     while (remaining > 0) {
       const int L = max(__ldg(p.seq_lens + s), 0);
       const int nt = (L + kTileTokens - 1) / kTileTokens;
       const int n = min(remaining, nt - tile);
-      // ---- query rows of this segment + its descriptor ----
-      const uint32_t slot = sg & 1;
-      mbar_wait(qempty_bar(slot), ((sg >> 1) & 1) ^ 1);
-      if (lane == 0) {
-        volatile int* d = desc + slot * 8;
-        d[0] = s; d[1] = hv; d[2] = tile; d[3] = n; d[4] = L;
-        mbar_arrive_expect_tx(qfull_bar(slot), (uint32_t)p.G * kD * 2);
-      }
-      __syncwarp();
-      if (lane < p.G) {
-        const uint16_t* src = qptr + (int64_t)s * p.q_stride_t + (int64_t)(hv * p.G + lane) * p.q_stride_h;
-        bulk_load_1d(q_base + slot * kQSlotBytes + lane * (kD * 2), src, kD * 2, qfull_bar(slot));
-      }
-      // ---- K/V tiles ----
       const int kvh = hv / p.gsplit;
-      const int32_t* bt = p.block_table + (int64_t)s * p.bt_stride;
+      const int row = p.row_map ? __ldg(p.row_map + s) : s;
+      const int32_t* bt = p.block_table + (int64_t)row * p.bt_stride;
+      const int pfx = __ldg(p.plan + kPlanPrefixOffset + s);
+      const uint32_t slot = sg & 1;
+      bool q_issued = false;
       int blk = 0;
-      for (int tt = 0; tt < n; ++tt) {
+      for (int tt = 0; tt <= n; ++tt) {
+        // ---- (once per segment, as soon as we are past the wait) query rows + segment descriptor ----
+        const bool early_ok = !waited && early_left > 0 && tt < n && (tile + tt + 1) * kTileTokens <= L - p.fresh;
+        if (!early_ok && !waited) {
+          pdl_wait();
+          waited = true;
+        }
+        if (waited && !q_issued) {
+          mbar_wait(qempty_bar(slot), ((sg >> 1) & 1) ^ 1);
+          if (lane == 0) {
+            volatile int* d = desc + slot * 8;
+            d[0] = s; d[1] = hv; d[2] = tile; d[3] = n; d[4] = L; d[5] = pfx;
+            mbar_arrive_expect_tx(qfull_bar(slot), (uint32_t)p.G * kD * 2);
+          }
+          __syncwarp();
+          if (lane < p.G) {
+            const uint16_t* src = qptr + (int64_t)s * p.q_stride_t + (int64_t)(hv * p.G + lane) * p.q_stride_h;
+            bulk_load_1d(q_base + slot * kQSlotBytes + lane * (kD * 2), src, kD * 2, qfull_bar(slot));
+          }
+          q_issued = true;
+        }
+        if (tt == n) break;
+        if (early_ok) --early_left;
+        // ---- K/V tile ----
         const int tl = tile + tt;
         if ((tt & 7) == 0) {  // refill 32 block ids (8 tiles) with one coalesced load
           const int ci = (tl << 2) + lane;
@@ -216,9 +240,11 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
         }
       }
     }
+    if (!waited) pdl_wait();
     return;
   }
 
+  // Consumers never run ahead of the wait: they block on the Q barrier, which the producer arms after it.
   // ============================================= consumers =============================================
   // MMA roles (mma.sync m16n8k16, fp32 accumulate):
   //   S^T(16 tok x 8 heads) = K(16 tok x d) . Q^T(d x 8 heads)     A = K rows straight from the swizzled tile
@@ -226,6 +252,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   // so the GQA group sits on the N side (8 or 2x8 heads, no padding rows) and a thread owns the softmax statistics
   // of exactly the heads (2t, 2t+1) whose O^T columns it accumulates.  P^T goes from the S^T accumulator layout to the
   // B-operand layout with two movmatrix.trans per 8 heads.
+  pdl_wait();
   const int w = warp;
   const int g = lane >> 2;
   const int t = lane & 3;
@@ -243,6 +270,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     const int tile0 = desc[slot * 8 + 2];
     const int n = desc[slot * 8 + 3];
     const int L = desc[slot * 8 + 4];
+    const int pfx = desc[slot * 8 + 5];
     const int kvh = hv / p.gsplit;
 
     // ---- Q fragments (B operand: n = head g (+8), k = permuted head-dim) ----
@@ -487,10 +515,10 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
       }
     }
     named_bar_sync(1, kConsumerWarps * 32);
+    const bool whole = (tile0 == 0) && ((tile0 + n) * kTileTokens >= L);
+    const float vscale = kFp8 ? __ldg(p.v_scale + (int64_t)kvh * p.scale_stride) : 1.0f;
     {
-      const bool whole = (tile0 == 0) && ((tile0 + n) * kTileTokens >= L);
       const int pslot = sg == 0 ? 0 : 1;
-      const float vscale = kFp8 ? __ldg(p.v_scale + (int64_t)kvh * p.scale_stride) : 1.0f;
       const int d = tid;  // 128 consumer threads <-> 128 head dims
       for (int head = 0; head < p.G; ++head) {
         float mg = ninf;
@@ -512,10 +540,122 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
             p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
         } else {
           const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + head;
-          p.ws_o[pidx * kD + d] = acc;
-          if (d == 0) {
-            p.ws_ml[pidx * 2 + 0] = mg;
-            p.ws_ml[pidx * 2 + 1] = lg;
+          __stcg(p.ws_o + pidx * kD + d, acc);
+          if (d == 0) __stcg(reinterpret_cast<float2*>(p.ws_ml + pidx * 2), make_float2(mg, lg));
+        }
+      }
+    }
+    // ---------------- in-kernel merge: the last CTA to deliver a partial of this (sequence, kv head) pair reduces them ----------------
+    if (!whole && p.fused_merge) {
+      named_bar_sync(1, kConsumerWarps * 32);  // all partial stores of this CTA are issued ...
+      volatile int* hand = desc + 16;
+      if (tid == 0) {
+        const int tpc = __ldg(p.plan + 1);
+        const int nt = (L + kTileTokens - 1) / kTileTokens;
+        const long long x0 = (long long)pfx * p.Hv + (long long)hv * nt;
+        const int c_lo = (int)(x0 / tpc), c_hi = (int)((x0 + nt - 1) / tpc);
+        const int slot_lo = (x0 == (long long)c_lo * tpc) ? 0 : 1;
+        int* cnt = p.plan + kPlanCounterOffset + c_lo * 2 + slot_lo;
+        const int np = c_hi - c_lo + 1;
+        __threadfence();  // ... and (cumulatively, through the barrier) made visible device-wide before the arrival counts
+        const int old = atomicAdd(cnt, 1);
+        const bool last = (old == np - 1);
+        if (last) {
+          *cnt = 0;         // every partial of the pair has arrived: re-arm the counter for the next launch
+          __threadfence();  // acquire side of the hand-shake
+        }
+        hand[0] = last ? np : 0;
+        hand[1] = c_lo;
+        hand[2] = slot_lo;
+      }
+      named_bar_sync(1, kConsumerWarps * 32);
+      const int np = hand[0];
+      if (np > 0) {
+        const int c_lo = hand[1], slot_lo = hand[2];
+        auto part = [&](int i, int head) { return ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head; };
+        constexpr int CH = NT == 1 ? 4 : 2;   // partials merged per round with every load in flight at once
+        constexpr int GH = NT * 8;
+        const int d = tid;
+        using E = Elem<QDT>;
+        if (np <= CH) {
+          // fast path (the common case: a pair cut by one to three CTA boundaries).  One round trip to L2: issue the
+          // partial-output loads first, then the (m, l) loads, then combine.
+          float ov[CH][GH];
+#pragma unroll
+          for (int i = 0; i < CH; ++i)
+#pragma unroll
+            for (int h = 0; h < GH; ++h) ov[i][h] = (i < np && h < p.G) ? ldcg_f32(p.ws_o + part(i, h) * kD + d) : 0.f;
+          {
+            const int head = tid >> 3, i = tid & 7;   // 8 lanes per head, lane i <-> partial i
+            float2 ml = make_float2(ninf, 0.f);
+            if (head < p.G && i < np) ml = ldcg_f32x2(p.ws_ml + part(i, head) * 2);
+            float mg = ml.x;
+#pragma unroll
+            for (int off = 1; off < 8; off <<= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
+            const float wgt = (ml.x == ninf) ? 0.f : fast_exp2(ml.x - mg);
+            float lg = ml.y * wgt;
+#pragma unroll
+            for (int off = 1; off < 8; off <<= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
+            if (head < p.G && i < CH) red_o[head * CH + i] = wgt * (vscale / lg);   // normalised weight of partial i
+            if (head < p.G && i == 0) red_ml[head] = (mg + fast_log2(lg)) * 0.6931471805599453f;
+          }
+          named_bar_sync(1, kConsumerWarps * 32);
+#pragma unroll
+          for (int h = 0; h < GH; ++h) {
+            if (h < p.G) {
+              float acc = 0.f;
+#pragma unroll
+              for (int i = 0; i < CH; ++i) acc += red_o[h * CH + i] * ov[i][h];   // weights of absent partials are 0
+              const int hq = hv * p.G + h;
+              typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+              op[d] = E::from_float(acc);
+              if (p.lse_out != nullptr && d == 0) p.lse_out[(int64_t)s * p.Hq + hq] = red_ml[h];
+            }
+          }
+        } else {
+          // general path: any number of partials (small batches with very long contexts)
+          {
+            const int head = tid >> 3, sub = tid & 7;
+            float mg = ninf, lg = 0.f;
+            if (head < p.G)
+              for (int i = sub; i < np; i += 8) mg = fmaxf(mg, ldcg_f32(p.ws_ml + part(i, head) * 2));
+#pragma unroll
+            for (int off = 1; off < 8; off <<= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
+            if (head < p.G)
+              for (int i = sub; i < np; i += 8) {
+                const float2 ml = ldcg_f32x2(p.ws_ml + part(i, head) * 2);
+                lg += (ml.x == ninf) ? 0.f : ml.y * fast_exp2(ml.x - mg);
+              }
+#pragma unroll
+            for (int off = 1; off < 8; off <<= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
+            if (sub == 0 && head < p.G) {
+              red_ml[head * 2 + 0] = mg;
+              red_ml[head * 2 + 1] = lg;
+            }
+          }
+          named_bar_sync(1, kConsumerWarps * 32);
+          float acc[GH];
+#pragma unroll
+          for (int h = 0; h < GH; ++h) acc[h] = 0.f;
+          for (int i = 0; i < np; ++i) {
+            float ov[GH], mv[GH];
+#pragma unroll
+            for (int h = 0; h < GH; ++h) {
+              ov[h] = h < p.G ? ldcg_f32(p.ws_o + part(i, h) * kD + d) : 0.f;
+              mv[h] = h < p.G ? ldcg_f32(p.ws_ml + part(i, h) * 2) : ninf;
+            }
+#pragma unroll
+            for (int h = 0; h < GH; ++h) acc[h] += (mv[h] == ninf ? 0.f : fast_exp2(mv[h] - red_ml[(h < p.G ? h : 0) * 2])) * ov[h];
+          }
+#pragma unroll
+          for (int h = 0; h < GH; ++h) {
+            if (h < p.G) {
+              const float mg = red_ml[h * 2 + 0], lg = red_ml[h * 2 + 1];
+              const int hq = hv * p.G + h;
+              typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+              op[d] = E::from_float(acc[h] * (vscale / lg));
+              if (p.lse_out != nullptr && d == 0) p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
+            }
           }
         }
       }
@@ -568,7 +708,7 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stri
                                int32_t num_kv_heads, int32_t head_dim, int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
                                float sm_scale, const float* k_scale, const float* v_scale, int32_t scale_stride,
                                const void* plan, int32_t num_ctas, void* workspace, size_t workspace_bytes,
-                               float* lse_out, void* stream) {
+                               float* lse_out, const int32_t* row_map, int32_t fresh_tokens, int32_t flags, void* stream) {
   if (num_seqs == 0) return B200ATTN_OK;
   if (!q || !out || !k_cache || !v_cache || !block_table || !seq_lens || !plan || !workspace) {
     set_error("decode: null pointer argument");
@@ -636,7 +776,10 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stri
   p.out = out; p.out_stride_t = out_stride_t; p.out_stride_h = out_stride_h;
   p.block_table = block_table; p.bt_stride = block_table_stride;
   p.seq_lens = seq_lens;
-  p.plan = reinterpret_cast<const int32_t*>(plan);
+  p.plan = reinterpret_cast<int32_t*>(const_cast<void*>(plan));
+  p.row_map = row_map;
+  p.fresh = fresh_tokens;
+  p.fused_merge = (flags & B200ATTN_DECODE_FUSED_MERGE) ? 1 : 0;
   p.ws_o = reinterpret_cast<float*>(workspace);
   p.ws_ml = p.ws_o + ws_o_floats(num_ctas, kD);
   p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;

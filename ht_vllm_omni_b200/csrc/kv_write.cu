@@ -51,9 +51,11 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
   const int64_t row = gid / lanes_per_row;
   const int col = (int)(gid - row * lanes_per_row) << 4;
   const int64_t rows = (int64_t)p.T * 2 * p.Hkv;
-  // Dependent-launch: everything above is index math; wait for the producer of key/value here.
-  pdl_wait();
+  // Dependent launch: let the decode kernel that follows become resident right away (it prefetches K/V tiles that
+  // this kernel cannot touch and only then waits for us); everything above is index math, wait for the producer of
+  // key/value here.
   pdl_launch_dependents();
+  pdl_wait();
   if (row >= rows) return;
   const int h = (int)(row % p.Hkv);
   const int kv = (int)((row / p.Hkv) & 1);

@@ -18,10 +18,12 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
                                                    int32_t* __restrict__ plan) {
   __shared__ int warp_sums[8];
   __shared__ int carry_s;
+  // No early griddepcontrol.launch_dependents here: kernels that follow may read the plan BEFORE their own
+  // griddepcontrol.wait (decode prefetches K/V tiles early), so they must not start until this grid has completed.
   pdl_wait();
-  pdl_launch_dependents();
   int32_t* prefix = plan + kPlanPrefixOffset;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = tid; i < kPlanCounterWords; i += 256) plan[kPlanCounterOffset + i] = 0;
   if (tid == 0) carry_s = 0;
   __syncthreads();
   for (int base = 0; base < B; base += 256) {

@@ -16,7 +16,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from ._lib import DT_BF16, DT_FP16, DT_FP8_E4M3, B200AttnError, check, load_library
+from ._lib import DECODE_FUSED_MERGE, DT_BF16, DT_FP16, DT_FP8_E4M3, B200AttnError, check, load_library
 
 _FP8_DTYPES = (torch.uint8, torch.float8_e4m3fn)
 
@@ -132,16 +132,20 @@ def _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale):
 
 
 def launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
-                        num_ctas, lse=None) -> None:
-    """Kernel 2 only (b200attn_decode): final rows for unsplit sequences, (o, m, l) partials for the rest."""
+                        num_ctas, lse=None, row_map=None, fresh_tokens=-1, fused_merge=False) -> None:
+    """Kernel 2 (b200attn_decode): final rows for unsplit sequences; split ones leave (o, m, l) partials that are merged
+    in-kernel by the last-arriving CTA (`fused_merge`) or by a following launch_merge."""
     (sb, ss, sh), kvdt, sstride = _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale)
+    if row_map is not None and (row_map.dtype != torch.int32 or not row_map.is_contiguous() or row_map.shape[0] != seq_lens.shape[0]):
+        raise B200AttnError("row_map must be contiguous int32 [num_rows]")
     check(load_library().b200attn_decode(
         query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1),
         k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, k_cache.shape[0], block_table.data_ptr(), block_table.stride(0),
         seq_lens.data_ptr(), seq_lens.shape[0], query.shape[1], k_cache.shape[2], query.shape[2], k_cache.shape[1],
         _dt(query), kvdt, float(sm_scale), k_scale.data_ptr(), v_scale.data_ptr(), sstride, plan.data_ptr(), num_ctas,
-        workspace.data_ptr(), workspace.numel() * 4, lse.data_ptr() if lse is not None else None, _stream(query)),
-        "b200attn_decode")
+        workspace.data_ptr(), workspace.numel() * 4, lse.data_ptr() if lse is not None else None,
+        row_map.data_ptr() if row_map is not None else None, int(fresh_tokens), DECODE_FUSED_MERGE if fused_merge else 0,
+        _stream(query)), "b200attn_decode")
 
 
 def launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse=None) -> None:
@@ -155,24 +159,30 @@ def launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse
         lse.data_ptr() if lse is not None else None, _stream(out)), "b200attn_merge")
 
 
-@torch.library.custom_op("b200attn::paged_decode", mutates_args=("out", "workspace", "lse"), device_types="cuda")
+@torch.library.custom_op("b200attn::paged_decode", mutates_args=("out", "plan", "workspace", "lse"), device_types="cuda")
 def paged_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
                  seq_lens: torch.Tensor, out: torch.Tensor, plan: torch.Tensor, workspace: torch.Tensor,
                  k_scale: torch.Tensor, v_scale: torch.Tensor, sm_scale: float, num_ctas: int,
-                 lse: torch.Tensor) -> None:
+                 lse: torch.Tensor, row_map: torch.Tensor, fresh_tokens: int = -1, fused_merge: bool = True) -> None:
     """`lse`: fp32 [B, Hq] to receive the natural-log LSE, or an EMPTY tensor to skip it (a required argument:
-    optional mutable tensors trip torch.library's version-counter bump when omitted)."""
+    optional mutable tensors trip torch.library's version-counter bump when omitted).  `row_map`: int32 [B] block-table
+    row of each decode row, or EMPTY for the identity.  `fresh_tokens`: see include/b200attn.h (-1 = unknown).
+    `fused_merge`: merge split-KV partials inside the decode kernel (default) instead of launching the merge kernel.
+    `plan` is listed as mutated because the in-kernel merge keeps its arrival counters there."""
     _require_cuda(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace)
     if seq_lens.shape[0] == 0:
         return
     lse = lse if lse.numel() > 0 else None
+    row_map = row_map if row_map.numel() > 0 else None
     launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
-                        num_ctas, lse)
-    launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse)
+                        num_ctas, lse, row_map, fresh_tokens, fused_merge)
+    if not fused_merge:
+        launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse)
 
 
 @paged_decode.register_fake
-def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale, num_ctas, lse) -> None:
+def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale, num_ctas, lse,
+      row_map, fresh_tokens=-1, fused_merge=True) -> None:
     return None
 
 
@@ -211,12 +221,15 @@ class DecodeWorkspace:
         self.plan = torch.zeros(plan_numel(max_num_seqs), dtype=torch.int32, device=self.device)
         self.workspace = torch.empty(workspace_numel(head_dim, self.num_ctas), dtype=torch.float32, device=self.device)
         self._no_lse = torch.empty(0, dtype=torch.float32, device=self.device)
+        self._no_map = torch.empty(0, dtype=torch.int32, device=self.device)
 
     def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int) -> None:
         if seq_lens.shape[0] > self.max_num_seqs:
             raise B200AttnError(f"batch {seq_lens.shape[0]} exceeds planned max_num_seqs {self.max_num_seqs}")
         torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.num_ctas)
 
-    def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None) -> None:
+    def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None,
+               row_map=None, fresh_tokens: int = -1, fused_merge: bool = True) -> None:
         torch.ops.b200attn.paged_decode(query, k_cache, v_cache, block_table, seq_lens, out, self.plan, self.workspace,
-                                        k_scale, v_scale, sm_scale, self.num_ctas, self._no_lse if lse is None else lse)
+                                        k_scale, v_scale, sm_scale, self.num_ctas, self._no_lse if lse is None else lse,
+                                        self._no_map if row_map is None else row_map, fresh_tokens, fused_merge)

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 1
+#define B200ATTN_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -46,6 +46,9 @@ extern "C" {
 #define B200ATTN_EINVAL (-1)  /* bad argument / unsupported shape */
 #define B200ATTN_ECUDA (-2)   /* CUDA runtime / driver error (incl. no device) */
 #define B200ATTN_ENOSPACE (-3) /* plan or workspace buffer too small */
+
+/* b200attn_decode flags */
+#define B200ATTN_DECODE_FUSED_MERGE 1 /* merge split-KV partials inside the decode kernel (no b200attn_merge call) */
 
 /* geometry constants the host side needs */
 #define B200ATTN_TILE_TOKENS 64 /* scheduling granule of the split-KV decode kernel */
@@ -108,11 +111,19 @@ B200ATTN_API size_t b200attn_workspace_bytes(int32_t head_dim, int32_t num_ctas)
  *   and kernel_unified_attention ($VLLM/v1/attention/ops/triton_unified_attention.py:178-643).
  *
  * out[b][hq][:] = softmax(sm_scale * k_scale * q[b][hq] . K[b][hq/G]^T) . V[b][hq/G] * v_scale over the
- * first seq_lens[b] tokens addressed through block_table[b][*].  Sequences whose whole range falls
- * inside one CTA are written to `out` directly; the others leave (o, m, l) partials in `workspace`
- * for b200attn_merge.  q/out dtype = q_dtype; kv_dtype fp8 accepts either q dtype, 16-bit KV must
- * equal q_dtype.  head_dim must be 128; block_size a multiple of 16.
- * The K/V planes are read through TMA: base pointers and byte strides must be 16-byte aligned.
+ * first seq_lens[b] tokens addressed through block_table[row(b)][*], row(b) = row_map ? row_map[b] : b
+ * (row_map lets several decode rows -- the query tokens of one request in a spec-decode / chunked-prefill
+ * batch, each with its own causal seq_len -- share one block-table row).  Sequences whose whole range falls
+ * inside one CTA are written to `out` directly; the others leave (o, m, l) partials in `workspace`.  With
+ * B200ATTN_DECODE_FUSED_MERGE the last CTA to deliver a partial of a pair reduces them in-kernel (arrival
+ * counters live in the plan buffer); without it b200attn_merge must follow.
+ * q/out dtype = q_dtype; kv_dtype fp8 accepts either q dtype, 16-bit KV must equal q_dtype.  head_dim must be
+ * 128; block_size a multiple of 16.  The K/V planes are read through TMA: base pointers and byte strides
+ * must be 16-byte aligned.
+ * fresh_tokens: upper bound on how many TRAILING positions of any row the kernel launched immediately before
+ * this one on `stream` may have written (1 for a decode step's KV write, max_query_len in general); K/V tiles
+ * below seq_len - fresh_tokens are prefetched before the programmatic-dependent-launch wait.  Pass -1 when
+ * unknown (e.g. the preceding kernel filled the whole cache): nothing is read early.
  */
 B200ATTN_API int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stride_h,
                     void* out, int64_t out_stride_t, int64_t out_stride_h,
@@ -128,13 +139,15 @@ B200ATTN_API int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_st
                     const void* plan, int32_t num_ctas,
                     void* workspace, size_t workspace_bytes,
                     float* lse_out /* nullable, [num_seqs][num_q_heads] natural-log LSE */,
+                    const int32_t* row_map /* nullable, [num_seqs] */, int32_t fresh_tokens, int32_t flags,
                     void* stream);
 
 /*
  * Kernel 3 — merge of split-KV partials (online-softmax reduction with warp shuffles).
  * Replaces: reduce_segments ($VLLM/v1/attention/ops/triton_unified_attention.py:645-733) and the
  *   in-kernel reduction of the TRT-LLM-gen "MultiCtasKv" cubins.
- * Must follow b200attn_decode on the same stream with the same plan / num_ctas / workspace / out.
+ * Must follow a b200attn_decode launched WITHOUT B200ATTN_DECODE_FUSED_MERGE on the same stream with the same
+ * plan / num_ctas / workspace / out.
  */
 B200ATTN_API int b200attn_merge(const void* plan, int32_t num_ctas, const void* workspace,
                    void* out, int64_t out_stride_t, int64_t out_stride_h,

@@ -65,9 +65,9 @@ def test_only_sm100a_code_is_embedded():
 
 
 def test_version_and_geometry(lib):
-    assert lib.b200attn_abi_version() == 1
+    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 2
     assert _lib.TILE_TOKENS == 64 and _lib.MAX_GROUP == 16
-    assert lib.b200attn_plan_bytes(64) >= (8 + 1024 * 4 + 65) * 4
+    assert lib.b200attn_plan_bytes(64) >= (8 + 1024 * 4 + 1024 * 2 + 65) * 4
     assert lib.b200attn_plan_bytes(64) % 16 == 0
     # workspace = [ctas][2][16][D] fp32 partial outputs + [ctas][2][16][2] fp32 (m, l)
     assert lib.b200attn_workspace_bytes(128, 296) == (296 * 2 * 16 * 128 + 296 * 2 * 16 * 2) * 4

@@ -21,7 +21,7 @@ def main():
     ap.add_argument("--Hq", type=int, default=16); ap.add_argument("--Hkv", type=int, default=2)
     ap.add_argument("--kv", default="fp8"); ap.add_argument("--layers", type=int, default=8)
     ap.add_argument("--ctas", default="0"); ap.add_argument("--debug", default="0"); ap.add_argument("--pdl", type=int, default=0)
-    ap.add_argument("--reps", type=int, default=5); ap.add_argument("--ragged", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=0); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--ragged", type=int, default=0)
     a = ap.parse_args()
     dev = torch.device("cuda")
     lib = ops.load_library()
@@ -71,6 +71,42 @@ def main():
             tm = timed(lambda l: ops.launch_merge(caches[l][0], d_lens, out, ws.plan, ws.workspace, vs, ws.num_ctas))
             tw = timed(lambda l: torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs))
             tall = timed(lambda l: (torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs), ws.decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ks, vs, D ** -0.5)))
+            if a.graph:
+                def graph_time(body, iters=10):
+                    side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(side):
+                        body()
+                    torch.cuda.current_stream().wait_stream(side); torch.cuda.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        body()
+                    for _ in range(3):
+                        g.replay()
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    for _ in range(iters):
+                        g.replay()
+                    e1.record(); torch.cuda.synchronize()
+                    return e0.elapsed_time(e1) * 1e3 / iters / a.layers
+                dec = lambda l: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.num_ctas)
+                mrg = lambda l: ops.launch_merge(caches[l][0], d_lens, out, ws.plan, ws.workspace, vs, ws.num_ctas)
+                wrt = lambda l: torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs)
+                for pdl in (0, 1):
+                    lib.b200attn_set_option(b"pdl", pdl)
+                    t_d = graph_time(lambda: [dec(l) for l in range(a.layers)])
+                    t_dm = graph_time(lambda: [(dec(l), mrg(l)) for l in range(a.layers)])
+                    t_wdm = graph_time(lambda: [(wrt(l), dec(l), mrg(l)) for l in range(a.layers)])
+                    decf = lambda l, fr: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.num_ctas, None, None, fr, True)
+                    t_f = graph_time(lambda: [decf(l, -1) for l in range(a.layers)])
+                    t_wf = graph_time(lambda: [(wrt(l), decf(l, -1)) for l in range(a.layers)])
+                    t_wf1 = graph_time(lambda: [(wrt(l), decf(l, 1)) for l in range(a.layers)])
+                    print(f"  graph/layer pdl={pdl}: FUSED-merge decode {t_f:.2f} | write+fused {t_wf:.2f} | write+fused(fresh=1, early prefetch) {t_wf1:.2f} us => all {(dec_b + wr_b) / t_wf1 / 1e3:.0f} GB/s", flush=True)
+                    t_w = graph_time(lambda: [wrt(l) for l in range(a.layers)])
+                    t_m = graph_time(lambda: [mrg(l) for l in range(a.layers)])
+                    print(f"  graph/layer pdl={pdl}: decode {t_d:.2f} | decode+merge {t_dm:.2f} | write+decode+merge {t_wdm:.2f} | write only {t_w:.2f} | merge only {t_m:.2f} us"
+                          f"  => decode {dec_b / t_d / 1e3:.0f} GB/s, all {(dec_b + wr_b) / t_wdm / 1e3:.0f} GB/s", flush=True)
+                lib.b200attn_set_option(b"pdl", a.pdl)
             print(f"B={B} L={L} ({Hq},{Hkv}) {a.kv} ctas={ws.num_ctas} debug={dbg} pdl={a.pdl} | decode mean {td[0]:.2f} med {td[1]:.2f} min {td[2]:.2f} us "
                   f"= {dec_b / td[1] / 1e3:.0f} GB/s | merge {tm[1]:.2f} us | kv_write {tw[1]:.2f} us | write+decode+merge {tall[1]:.2f} us", flush=True)
     lib.b200attn_set_option(b"debug", 0)
