@@ -65,49 +65,83 @@ def load_peaks():
 # clocks sampler (nvidia-smi during the timed region)
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
-    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """Polls NVML (pynvml) every 2 ms from a thread while `active`; falls back to `nvidia-smi -lms 20` when NVML is missing."""
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.samples = []
-        self.proc = None
+        self.samples = []   # (sm_mhz, sm_max_mhz, reasons bitmask)
         self.active = False
+        self._stop = False
+        self._thread = None
+        self._max = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
-                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except Exception:  # noqa: BLE001
-            self.proc = None
-            return
-        threading.Thread(target=self._reader, daemon=True).start()
+            import pynvml
+            pynvml.nvmlInit()
+            # honour CUDA_VISIBLE_DEVICES: map the CUDA ordinal to the NVML device through its UUID
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+            try:
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:  # noqa: BLE001
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            self._max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": pynvml.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": pynvml.nvmlClocksThrottleReasonSwPowerCap}
 
-    def _reader(self):
-        for line in self.proc.stdout:
-            if self.active:
-                self.samples.append(line.strip())
+            def poll():
+                while not self._stop:
+                    if self.active:
+                        try:
+                            mhz = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                            r = int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                            self.samples.append((mhz, self._max, [n for n, b in bits.items() if r & b]))
+                        except Exception:  # noqa: BLE001
+                            pass
+                    time.sleep(0.002)
+        except Exception:  # noqa: BLE001
+            fields = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+                      "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+                      "clocks_event_reasons.sw_power_cap")
+            try:
+                proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={fields}", "--format=csv,noheader,nounits", "-lms", "20",
+                                         "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            except Exception:  # noqa: BLE001
+                return
+            self._proc = proc
+
+            def poll():
+                for line in proc.stdout:
+                    if self._stop:
+                        break
+                    if not self.active:
+                        continue
+                    f = [x.strip() for x in line.split(",")]
+                    try:
+                        self.samples.append((float(f[1]), float(f[2]),
+                                             [n for n, v in zip(self.NAMES, f[4:8]) if v.lower().startswith("active")]))
+                    except Exception:  # noqa: BLE001
+                        continue
+        self._thread = threading.Thread(target=poll, daemon=True)
+        self._thread.start()
 
     def stop(self):
-        if self.proc is not None:
-            self.proc.terminate()
+        self._stop = True
+        proc = getattr(self, "_proc", None)
+        if proc is not None:
+            proc.terminate()
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        for s in self.samples:
-            p = [x.strip() for x in s.split(",")]
-            try:
-                sm.append(float(p[1])); mx.append(float(p[2]))
-            except Exception:  # noqa: BLE001
-                continue
-            for name, val in zip(self.NAMES, p[4:8]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
+        if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        sm = [s[0] for s in self.samples]
+        reasons = sorted({r for s in self.samples for r in s[2]})
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(s[1] for s in self.samples)), "reasons": reasons,
+                "samples": len(sm)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -255,7 +289,7 @@ def run_ours(args, w):
         if gathered is not None:
             dist.all_gather_into_tensor(gathered, out)
 
-    launches_per_step = 1 + 3 * NL
+    launches_per_step = 1 + 2 * NL   # plan + per layer: kv_write, decode (split-KV partials merged in-kernel)
 
     # ---- capture one step into a CUDA graph ----
     side = torch.cuda.Stream(device=dev)

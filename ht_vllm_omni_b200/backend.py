@@ -1,0 +1,312 @@
+"""vLLM attention-backend plugin surface for the B200 paged-decode path.
+
+ht-vllm-omni's AR stages (Qwen3-TTS talker, Qwen3-Omni thinker) reach paged attention only through vLLM's
+`AttentionBackend` / `AttentionMetadataBuilder` / `AttentionImpl` triple ($VLLM/v1/attention/backend.py:55-342,
+516-663, 763-840; caller: vllm_omni/worker/gpu_ar_model_runner.py:228-298).  This module provides that triple over
+`torch.ops.b200attn.*` (ops.py -> libb200attn.so), so the hot path is swapped by *registration*, not by editing the
+reference:
+
+    register_backend(AttentionBackendEnum.CUSTOM, "ht_vllm_omni_b200.backend.B200PagedAttentionBackend")
+
+and `attention_backend: CUSTOM` in the stage's engine_args (`plugin.register()` does the call).
+
+What the reference does at each hook, and what we do instead:
+  * do_kv_cache_update  -> torch.ops._C_cache_ops.reshape_and_cache_flash ($VLLM/.../flashinfer.py:1828-1855)
+                         -> torch.ops.b200attn.kv_write (kernel 1)
+  * forward (decode)    -> trtllm_batch_decode_with_kv_cache / unified_attention (flashinfer.py:1751-1822,
+                           triton_attn.py:526-672)   -> torch.ops.b200attn.paged_decode (kernel 2 + in-kernel merge)
+  * MetadataBuilder.build -> FlashInfer `plan` / Triton segment buffers (flashinfer.py:886-1248, triton_attn.py:216-268)
+                         -> torch.ops.b200attn.decode_plan (device-side, sync-free) into buffers owned by the builder
+
+Rows with more than one query token (spec-decode verification, chunked prefill) are served by the same kernel: every
+query token becomes a decode row with its own causal length and a `row_map` entry pointing at its request's
+block-table row.  That keeps the backend a complete drop-in (correct for any batch vLLM schedules); a dedicated
+prefill kernel is a §8(f) "next" row.
+
+There is no fallback to another backend or to the CPU: without libb200attn.so / a CUDA device the ops raise.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import ClassVar
+
+import torch
+
+from vllm.v1.attention.backend import (
+    AttentionBackend,
+    AttentionCGSupport,
+    AttentionImpl,
+    AttentionLayer,
+    AttentionMetadataBuilder,
+    AttentionType,
+    CommonAttentionMetadata,
+    MultipleOf,
+)
+
+from . import ops
+from ._lib import B200AttnError
+
+BACKEND_PATH = "ht_vllm_omni_b200.backend.B200PagedAttentionBackend"
+_FP8_NAMES = ("fp8", "fp8_e4m3")
+
+
+def is_fp8_kv(kv_cache_dtype: str) -> bool:
+    return kv_cache_dtype in _FP8_NAMES
+
+
+def expand_query_rows(query_start_loc: torch.Tensor, seq_lens: torch.Tensor, num_tokens: int):
+    """Per-token decode rows for a batch with multi-token requests (no host sync; shapes depend only on num_tokens).
+
+    Token t of request r (tokens query_start_loc[r] .. query_start_loc[r+1]-1, the LAST one at position seq_lens[r]-1)
+    attends causally to the first `seq_lens[r] - (query_start_loc[r+1] - 1 - t)` cache positions: vLLM's
+    context_len + q_pos + 1 (triton_unified_attention.py:286-303).  Returns (row_seq_lens int32 [T], row_map int32 [T]).
+    Tokens past query_start_loc[-1] (CUDA-graph padding) get length 0, which the kernel skips.
+    """
+    t = torch.arange(num_tokens, device=query_start_loc.device, dtype=query_start_loc.dtype)
+    num_reqs = seq_lens.shape[0]
+    req = torch.bucketize(t, query_start_loc[1:num_reqs + 1], right=True)       # request of token t; == num_reqs for padding
+    pad = req >= num_reqs
+    req = req.clamp_max(num_reqs - 1)
+    last = query_start_loc[1:num_reqs + 1][req] - 1
+    lens = seq_lens[req].to(torch.int64) - (last.to(torch.int64) - t.to(torch.int64))
+    lens = torch.where(pad, torch.zeros_like(lens), lens.clamp_min(0))
+    return lens.to(torch.int32), req.to(torch.int32)
+
+
+class B200PagedAttentionBackend(AttentionBackend):
+    """Static description of the backend; mirrors FlashInferBackend's answers where the layout is shared
+    ($VLLM/v1/attention/backends/flashinfer.py:326-436)."""
+
+    accept_output_buffer: bool = True
+    supported_dtypes: ClassVar[list[torch.dtype]] = [torch.float16, torch.bfloat16]
+    supported_kv_cache_dtypes: ClassVar[list[str]] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3"]
+    # the KV write is its own custom op (unified_kv_cache_update), as the reference's runner expects
+    # (vllm_omni/worker/gpu_ar_model_runner.py:231-244)
+    forward_includes_kv_cache_update: bool = False
+
+    @staticmethod
+    def get_name() -> str:
+        return "CUSTOM"   # Attention.__init__ maps the name back through AttentionBackendEnum[...] (attention.py:386)
+
+    @staticmethod
+    def get_impl_cls() -> type["B200PagedAttentionImpl"]:
+        return B200PagedAttentionImpl
+
+    @staticmethod
+    def get_builder_cls() -> type["B200PagedAttentionMetadataBuilder"]:
+        return B200PagedAttentionMetadataBuilder
+
+    @staticmethod
+    def get_supported_kernel_block_sizes() -> list[int | MultipleOf]:
+        return [MultipleOf(16)]   # the TMA box is 16 tokens x 128 bytes; a page holds a whole number of boxes
+
+    @classmethod
+    def get_supported_head_sizes(cls) -> list[int]:
+        return [128]
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int,
+                           cache_dtype_str: str = "auto") -> tuple[int, ...]:
+        # logical shape shared with FlashInfer / Triton / FlashAttention-on-sm100 (flashinfer.py:357-368); the KV
+        # hand-off code of the reference indexes it as [block, 0|1, slot, head, dim]
+        # (vllm_omni/distributed/omni_connectors/kv_transfer_manager.py:224-301)
+        if block_size % 16 != 0:
+            raise ValueError("B200 paged attention needs block_size % 16 == 0")
+        return (num_blocks, 2, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def get_kv_cache_stride_order(include_num_layers_dimension: bool = False) -> tuple[int, ...]:
+        # HND physical order: [block][K|V][head][slot][dim] -> one (block, head) K page is bs*D contiguous bytes
+        if include_num_layers_dimension:
+            return (1, 2, 4, 0, 3, 5)   # (num_blocks, 2, num_kv_heads, num_layers, block_size, head_size)
+        return (0, 1, 3, 2, 4)
+
+    @classmethod
+    def get_required_kv_cache_layout(cls):
+        return "HND"
+
+    @classmethod
+    def supports_per_head_quant_scales(cls) -> bool:
+        return True
+
+    @classmethod
+    def supports_compute_capability(cls, capability) -> bool:
+        return getattr(capability, "major", None) == 10   # sm_100a cubins only
+
+    @classmethod
+    def supports_attn_type(cls, attn_type: str) -> bool:
+        return attn_type == AttentionType.DECODER
+
+    @classmethod
+    def supports_combination(cls, head_size, dtype, kv_cache_dtype, block_size, use_mla, has_sink, use_sparse,
+                             device_capability) -> str | None:
+        if kv_cache_dtype in ("float16", "bfloat16") and dtype is not None:
+            want = torch.float16 if kv_cache_dtype == "float16" else torch.bfloat16
+            if dtype != want:
+                return f"16-bit KV cache ({kv_cache_dtype}) must match the model dtype ({dtype})"
+        return None
+
+
+@dataclass
+class B200PagedAttentionMetadata:
+    """Per-step, per-KV-cache-group metadata.  All tensors are views of vLLM's persistent buffers or of the builder's
+    own pre-allocated buffers, so the object is CUDA-graph safe (capture and replay see the same addresses)."""
+
+    num_actual_tokens: int
+    num_rows: int                     # decode rows handed to the kernel (== tokens)
+    max_query_len: int
+    seq_lens: torch.Tensor            # int32 [num_rows]: causal length of each row
+    block_table: torch.Tensor         # int32 [num_reqs, max_blocks]
+    row_map: torch.Tensor | None      # int32 [num_rows] block-table row per decode row; None = identity (pure decode)
+    slot_mapping: torch.Tensor
+    workspace: "ops.DecodeWorkspace"  # plan + split-KV partial buffers (owned by the builder)
+    use_cascade: bool = False
+
+
+class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttentionMetadata]):
+    """Builds the split-KV plan once per step on the device (kernel `plan_kernel`, no host sync, no allocation)."""
+
+    _cudagraph_support: ClassVar[AttentionCGSupport] = AttentionCGSupport.ALWAYS
+    reorder_batch_threshold: int | None = None   # one kernel serves every row: no decode/prefill reordering needed
+
+    def __init__(self, kv_cache_spec, layer_names, vllm_config, device):
+        super().__init__(kv_cache_spec, layer_names, vllm_config, device)
+        model_config = vllm_config.model_config
+        parallel_config = vllm_config.parallel_config
+        self.block_size = kv_cache_spec.block_size
+        self.num_heads_q = model_config.get_num_attention_heads(parallel_config)
+        self.num_heads_kv = model_config.get_num_kv_heads(parallel_config)
+        self.head_dim = model_config.get_head_size()
+        kv_dtype = getattr(kv_cache_spec, "dtype", torch.bfloat16)
+        self.kv_torch_dtype = torch.uint8 if kv_dtype in (torch.uint8, torch.float8_e4m3fn) else kv_dtype
+        # rows = tokens: size every buffer for the largest batch vLLM can schedule
+        self.max_rows = int(vllm_config.scheduler_config.max_num_batched_tokens)
+        self.workspace = ops.DecodeWorkspace(device, self.max_rows, self.kv_torch_dtype, head_dim=self.head_dim)
+        self._row_lens = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
+        self._row_map = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
+
+    def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
+              fast_build: bool = False) -> B200PagedAttentionMetadata:
+        m = common_attn_metadata
+        T = m.num_actual_tokens
+        if T > self.max_rows:
+            raise B200AttnError(f"{T} tokens exceed the planned maximum of {self.max_rows}")
+        if m.max_query_len <= 1 and T == m.num_reqs:
+            seq_lens, row_map = m.seq_lens, None                    # pure decode: rows == requests
+        else:
+            lens, rmap = expand_query_rows(m.query_start_loc, m.seq_lens, T)
+            self._row_lens[:T].copy_(lens)
+            self._row_map[:T].copy_(rmap)
+            seq_lens, row_map = self._row_lens[:T], self._row_map[:T]
+        self.workspace.make_plan(seq_lens, self.num_heads_q, self.num_heads_kv)
+        return B200PagedAttentionMetadata(
+            num_actual_tokens=T, num_rows=T, max_query_len=m.max_query_len, seq_lens=seq_lens,
+            block_table=m.block_table_tensor, row_map=row_map, slot_mapping=m.slot_mapping, workspace=self.workspace)
+
+    def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200PagedAttentionMetadata:
+        # the plan kernel reads seq_lens on the device at replay time; nothing is baked in at capture
+        return self.build(0, common_attn_metadata)
+
+    def use_cascade_attention(self, *args, **kwargs) -> bool:
+        return False
+
+
+class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
+    can_return_lse_for_decode: bool = True   # b200attn_decode writes natural-log LSE (DCP combine, §8e)
+
+    def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int | None = None,
+                 alibi_slopes: list[float] | None = None, sliding_window: int | None = None,
+                 kv_cache_dtype: str = "auto", logits_soft_cap: float | None = None,
+                 attn_type: str = AttentionType.DECODER, kv_sharing_target_layer_name: str | None = None,
+                 sinks: torch.Tensor | None = None, **extra) -> None:
+        # unsupported features are rejected at construction (selection time), never on the hot path
+        if alibi_slopes is not None:
+            raise NotImplementedError("B200 paged attention: ALiBi is not supported")
+        if sliding_window is not None:
+            raise NotImplementedError("B200 paged attention: sliding window is not supported")
+        if logits_soft_cap:
+            raise NotImplementedError("B200 paged attention: logits soft cap is not supported")
+        if sinks is not None:
+            raise NotImplementedError("B200 paged attention: attention sinks are not supported")
+        if attn_type != AttentionType.DECODER:
+            raise NotImplementedError("B200 paged attention: decoder self-attention only")
+        if head_size != 128:
+            raise NotImplementedError(f"B200 paged attention: head_size {head_size} unsupported (128 only)")
+        if kv_cache_dtype not in B200PagedAttentionBackend.supported_kv_cache_dtypes:
+            raise NotImplementedError(f"B200 paged attention: kv_cache_dtype {kv_cache_dtype!r} unsupported")
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.scale = float(scale)
+        self.num_kv_heads = num_kv_heads if num_kv_heads is not None else num_heads
+        if self.num_heads % self.num_kv_heads != 0:
+            raise ValueError("num_heads must be a multiple of num_kv_heads")
+        self.num_queries_per_kv = self.num_heads // self.num_kv_heads
+        self.kv_cache_dtype = kv_cache_dtype
+        self.attn_type = attn_type
+        self.kv_sharing_target_layer_name = kv_sharing_target_layer_name
+        self.alibi_slopes = None
+        self.sliding_window = (-1, -1)
+        self.logits_soft_cap = 0.0
+        self.supports_quant_query_input = False   # Q stays bf16/fp16: K is expanded exactly in-kernel instead
+        self._unit_scale: torch.Tensor | None = None
+
+    # ---- helpers ----
+    def _planes(self, kv_cache: torch.Tensor):
+        """[num_blocks, 2, block_size, Hkv, D] (any strides) -> K and V planes [num_blocks, block_size, Hkv, D]."""
+        if kv_cache.dim() != 5 or kv_cache.shape[1] != 2:
+            raise B200AttnError(f"kv_cache must be [num_blocks, 2, block_size, Hkv, D], got {tuple(kv_cache.shape)}")
+        k, v = kv_cache.unbind(1)
+        if is_fp8_kv(self.kv_cache_dtype) and k.dtype not in (torch.uint8, torch.float8_e4m3fn):
+            k, v = k.view(torch.uint8), v.view(torch.uint8)
+        return k, v
+
+    def _scales(self, layer: AttentionLayer, device):
+        if is_fp8_kv(self.kv_cache_dtype):
+            return layer._k_scale, layer._v_scale     # fp32 device tensors, 1 or Hkv elements (attention.py:94-174)
+        if self._unit_scale is None or self._unit_scale.device != device:
+            self._unit_scale = torch.ones(1, dtype=torch.float32, device=device)
+        return self._unit_scale, self._unit_scale
+
+    # ---- hooks ----
+    def do_kv_cache_update(self, layer: AttentionLayer, key: torch.Tensor, value: torch.Tensor,
+                           kv_cache: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+        """Replaces reshape_and_cache_flash.  key/value are [T, Hkv, D] slices of the fused qkv activation (strided);
+        slot_mapping may be longer than the real token count under padding: -1 entries are skipped in-kernel."""
+        if self.kv_sharing_target_layer_name is not None:
+            return   # the target layer already wrote this cache (attention.py:700-706 semantics)
+        k_cache, v_cache = self._planes(kv_cache)
+        k_scale, v_scale = self._scales(layer, key.device)
+        n = min(slot_mapping.shape[0], key.shape[0])
+        torch.ops.b200attn.kv_write(key[:n].view(n, self.num_kv_heads, self.head_size),
+                                    value[:n].view(n, self.num_kv_heads, self.head_size),
+                                    k_cache, v_cache, slot_mapping[:n], k_scale, v_scale)
+
+    def forward(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                kv_cache: torch.Tensor, attn_metadata: B200PagedAttentionMetadata, output: torch.Tensor,
+                output_scale: torch.Tensor | None = None, output_block_scale: torch.Tensor | None = None) -> torch.Tensor:
+        assert output is not None, "output tensor must be provided (accept_output_buffer)"
+        if output_scale is not None or output_block_scale is not None:
+            raise NotImplementedError("B200 paged attention: fused output quantisation is not supported")
+        if attn_metadata is None:
+            return output.fill_(0)    # profiling run (triton_attn.py:557-559)
+        md = attn_metadata
+        T = md.num_actual_tokens
+        k_cache, v_cache = self._planes(kv_cache)
+        k_scale, v_scale = self._scales(layer, query.device)
+        q = query[:T].view(T, self.num_heads, self.head_size)
+        out = output[:T].view(T, self.num_heads, self.head_size)
+        # fresh_tokens: the KV write that precedes us on the stream touched at most the last max_query_len positions
+        md.workspace.decode(q, k_cache, v_cache, md.block_table, md.seq_lens, out, k_scale, v_scale, self.scale,
+                            row_map=md.row_map, fresh_tokens=max(1, md.max_query_len), fused_merge=True)
+        return output
+
+    def forward_with_lse(self, layer, query, kv_cache, attn_metadata, output, lse) -> None:
+        """Decode returning the natural-log LSE per (row, head): the per-rank piece of a sequence-split (DCP) exchange,
+        combined across ranks by torch.ops.b200attn.merge_lse (replaces cp_lse_ag_out_rs, flashinfer.py:1714-1738)."""
+        md = attn_metadata
+        T = md.num_actual_tokens
+        k_cache, v_cache = self._planes(kv_cache)
+        k_scale, v_scale = self._scales(layer, query.device)
+        md.workspace.decode(query[:T].view(T, self.num_heads, self.head_size), k_cache, v_cache, md.block_table,
+                            md.seq_lens, output[:T].view(T, self.num_heads, self.head_size), k_scale, v_scale,
+                            self.scale, lse=lse, row_map=md.row_map, fresh_tokens=max(1, md.max_query_len))

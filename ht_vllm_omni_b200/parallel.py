@@ -1,0 +1,140 @@
+"""Multi-GPU layout of the paged-decode path: KV-head sharding (vLLM's TP layout) and the sequence-split exchange
+used when there are more ranks than KV heads.  One process per GPU, torch.distributed (NCCL on the
+box, gloo in the CPU tests) for the plumbing; the arithmetic stays in libb200attn.
+
+Head sharding needs NO collective inside attention: rank r owns KV heads [r*Hkv/tp, (r+1)*Hkv/tp) with their G query
+heads, its own cache shard, and replicated block tables / seq_lens ($VLLM/model_executor/models/qwen3.py:78-95); the
+row-parallel o_proj that follows consumes head-sharded outputs.  `all_gather_heads` is the optional NCCL all-gather the
+north star names, for callers that want unsharded heads.
+
+With tp > Hkv vLLM replicates each KV head on tp/Hkv ranks (qwen3.py:88-91), so KV bytes per GPU stop shrinking.  The
+sequence-split ("DCP") remedy: the ranks of one replica group each keep every `dcp`-th token of the context
+($VLLM/v1/worker/block_table.py:148-162), all-gather the group's query heads (tiny), run the same decode kernel over
+their slice returning (o, lse), and combine by log-sum-exp (replaces cp_lse_ag_out_rs,
+$VLLM/v1/attention/backends/flashinfer.py:1714-1738) with `torch.ops.b200attn.merge_lse`.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass(frozen=True)
+class HeadShard:
+    """What one TP rank owns.  Query heads are always split evenly; a KV head is replicated when tp > Hkv."""
+
+    tp_size: int
+    tp_rank: int
+    total_q_heads: int
+    total_kv_heads: int
+
+    def __post_init__(self):
+        if self.total_q_heads % self.total_kv_heads:
+            raise ValueError("Hq must be a multiple of Hkv")
+        if self.total_q_heads % self.tp_size:
+            raise ValueError("Hq must be divisible by tp_size")
+        if self.tp_size <= self.total_kv_heads:
+            if self.total_kv_heads % self.tp_size:
+                raise ValueError("Hkv must be divisible by tp_size")
+        elif self.tp_size % self.total_kv_heads:
+            raise ValueError("tp_size must be a multiple of Hkv when it exceeds it")
+        if not 0 <= self.tp_rank < self.tp_size:
+            raise ValueError("tp_rank out of range")
+
+    @property
+    def num_q_heads(self) -> int:
+        return self.total_q_heads // self.tp_size
+
+    @property
+    def num_kv_heads(self) -> int:
+        return max(1, self.total_kv_heads // self.tp_size)
+
+    @property
+    def replicas(self) -> int:
+        """Ranks holding the same KV head (1 while tp <= Hkv): the size of a sequence-split group."""
+        return max(1, self.tp_size // self.total_kv_heads)
+
+    @property
+    def replica_rank(self) -> int:
+        return self.tp_rank % self.replicas
+
+    @property
+    def q_head_range(self) -> range:
+        return range(self.tp_rank * self.num_q_heads, (self.tp_rank + 1) * self.num_q_heads)
+
+    @property
+    def kv_head_range(self) -> range:
+        if self.tp_size <= self.total_kv_heads:
+            return range(self.tp_rank * self.num_kv_heads, (self.tp_rank + 1) * self.num_kv_heads)
+        h = self.tp_rank // self.replicas
+        return range(h, h + 1)
+
+    def replica_group_ranks(self) -> list[int]:
+        base = (self.tp_rank // self.replicas) * self.replicas
+        return list(range(base, base + self.replicas))
+
+
+def all_gather_heads(out_local: torch.Tensor, group=None) -> torch.Tensor:
+    """[T, Hq/tp, D] on every rank -> [T, Hq, D] (heads in rank order).  One all-gather, no other traffic."""
+    world = dist.get_world_size(group)
+    if world == 1:
+        return out_local
+    T, Hl, D = out_local.shape
+    buf = torch.empty((world * T, Hl, D), dtype=out_local.dtype, device=out_local.device)   # rank-major concat along dim 0
+    dist.all_gather_into_tensor(buf, out_local.contiguous(), group=group)
+    return buf.view(world, T, Hl, D).permute(1, 0, 2, 3).reshape(T, world * Hl, D)
+
+
+def dcp_local_seq_lens(seq_lens: torch.Tensor, dcp_size: int, dcp_rank: int, interleave: int = 1) -> torch.Tensor:
+    """Tokens of a context are dealt round-robin in runs of `interleave` to the ranks of a sequence-split group:
+    position p lives on rank (p // interleave) % dcp_size.  Returns how many of the first seq_lens[s] positions this rank
+    holds (int32, same device, no host sync) — the `seq_lens` its local decode call gets."""
+    L = seq_lens.to(torch.int64)
+    round_len = dcp_size * interleave
+    full = (L // round_len) * interleave
+    rem = (L % round_len) - dcp_rank * interleave
+    return (full + rem.clamp(0, interleave)).to(torch.int32)
+
+
+def dcp_local_positions(seq_len: int, dcp_size: int, dcp_rank: int, interleave: int = 1) -> list[int]:
+    """Host-side mirror of dcp_local_seq_lens: the global positions a rank holds, in local order."""
+    return [p for p in range(seq_len) if (p // interleave) % dcp_size == dcp_rank]
+
+
+def _cuda_merge_lse(parts_o, parts_lse, out, lse_out):
+    torch.ops.b200attn.merge_lse(parts_o, parts_lse, out, lse_out)   # raises on CPU tensors: no CPU fallback
+
+
+def dcp_gather_queries(q_local: torch.Tensor, group=None) -> torch.Tensor:
+    """All-gather the replica group's query heads: [T, Hq_local, D] -> [T, dcp*Hq_local, D] (all share one KV head)."""
+    return all_gather_heads(q_local, group)
+
+
+def dcp_combine(out_part: torch.Tensor, lse_part: torch.Tensor, group=None, merge_fn=None,
+                keep_local_heads: bool = True) -> torch.Tensor:
+    """Combine the per-rank partial attention of a sequence-split group.
+
+    out_part [T, Hg, D] / lse_part [T, Hg] fp32 (natural log; -inf where the rank held no token) are this rank's result
+    for ALL Hg = dcp*Hq_local heads of the group over ITS slice of the context.  All-gathers both, merges by
+    log-sum-exp (`merge_fn`, default the CUDA kernel), and returns this rank's own Hq_local heads (or all Hg).
+    """
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    T, Hg, D = out_part.shape
+    merge = merge_fn or _cuda_merge_lse
+    parts_o = torch.empty((world, T, Hg, D), dtype=out_part.dtype, device=out_part.device)
+    parts_lse = torch.empty((world, T, Hg), dtype=torch.float32, device=out_part.device)
+    if world > 1:
+        dist.all_gather_into_tensor(parts_o.view(world * T, Hg, D), out_part.contiguous(), group=group)
+        dist.all_gather_into_tensor(parts_lse.view(world * T, Hg), lse_part.contiguous(), group=group)
+    else:
+        parts_o[0].copy_(out_part)
+        parts_lse[0].copy_(lse_part)
+    out = torch.empty((T, Hg, D), dtype=out_part.dtype, device=out_part.device)
+    merge(parts_o, parts_lse, out, torch.empty(0, dtype=torch.float32, device=out_part.device))
+    if not keep_local_heads:
+        return out
+    hl = Hg // world
+    return out[:, rank * hl:(rank + 1) * hl]

@@ -40,7 +40,8 @@ class Case:
 
         def rnd(*shape):
             if dist == "heavy":   # Student-t(3): exercises fp8 saturation
-                x = torch.randn(*shape, generator=g) / torch.sqrt(torch.distributions.Chi2(3.0).sample(shape) / 3.0)
+                chi2 = torch.randn(3, *shape, generator=g).square().sum(0)   # seeded (torch.distributions ignores `g`)
+                x = torch.randn(*shape, generator=g) / torch.sqrt(chi2 / 3.0)
                 return x.to(adt)
             return torch.randn(*shape, generator=g).to(adt)
 

@@ -39,7 +39,7 @@ def ops():
     return ops
 
 
-def run_case(ops, c, ctas=None, check_write=True, lse=False):
+def run_case(ops, c, ctas=None, check_write=True, lse=False, fused_merge=True):
     kc_o, vc_o = c.oracle_cache()
     torch.ops.b200attn.kv_write(c.d_key, c.d_value, c.kc, c.vc, c.d_slots, c.d_ks, c.d_vs)
     torch.cuda.synchronize()
@@ -50,7 +50,7 @@ def run_case(ops, c, ctas=None, check_write=True, lse=False):
     out = torch.full((c.B, c.Hq, c.D), float("nan"), dtype=c.d_q.dtype, device="cuda")
     d_lse = torch.zeros(c.B, c.Hq, dtype=torch.float32, device="cuda") if lse else None
     ws.make_plan(c.d_lens, c.Hq, c.Hkv)
-    ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale, d_lse)
+    ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale, d_lse, fused_merge=fused_merge)
     torch.cuda.synchronize()
     got = out.float().cpu().numpy()
     valid = c.lens > 0
@@ -100,6 +100,27 @@ LADDER = [
 def test_write_and_decode_match_oracle(ops, name, lens, Hq, Hkv, kv, act, ctas, extra):
     c = Case(lens, Hq, Hkv, kv=kv, act=act, **extra).cuda()
     run_case(ops, c, ctas=ctas)
+
+
+TWO_KERNEL = ["fp8_L1000_4cta_merge", "fp8_ragged_7cta", "fp8_ragged_empty_rows_default_grid", "fp8_G16", "fp8_G7_qwen2",
+              "fp8_G32_two_passes", "bf16_ragged_7cta", "fp16_kv_and_act", "thinker_heads_32_4"]
+
+
+@pytest.mark.parametrize("name", TWO_KERNEL)
+def test_split_decode_then_merge_kernel(ops, name):
+    """Same ladder rows through the two-launch path (b200attn_decode without FUSED_MERGE, then b200attn_merge)."""
+    _, lens, Hq, Hkv, kv, act, ctas, extra = next(x for x in LADDER if x[0] == name)
+    c = Case(lens, Hq, Hkv, kv=kv, act=act, **extra).cuda()
+    run_case(ops, c, ctas=ctas, fused_merge=False)
+
+
+def test_fused_and_two_kernel_merge_agree_bitwise_on_unsplit_rows(ops):
+    """Rows that one CTA handles whole never touch the workspace: both paths must give identical bytes for them."""
+    c = Case([64, 64, 64, 64, 2000], 16, 2, kv="fp8").cuda()
+    a, _, _ = run_case(ops, c, ctas=24, fused_merge=True)
+    b, _, _ = run_case(ops, c, ctas=24, fused_merge=False, check_write=False)
+    assert np.array_equal(a[:4], b[:4])
+    assert np.abs(a[4] - b[4]).max() <= 2.0 ** -7 * max(1.0, float(np.abs(a[4]).max()))
 
 
 def test_lse_output_matches_oracle(ops):
