@@ -14,6 +14,7 @@ static thread_local char g_err[512] = "";
 static int g_opt_pdl = 1;
 static int g_opt_force_simt = 0;
 static int g_opt_debug = 0;
+static int g_opt_tc = 1;
 static unsigned long long* g_dbg_buf = nullptr;
 
 void set_error(const char* fmt, ...) {
@@ -32,6 +33,7 @@ int check_cuda(cudaError_t e, const char* what) {
 
 int option_force_simt() { return g_opt_force_simt; }
 int option_debug() { return g_opt_debug; }
+int option_tc() { return g_opt_tc; }
 unsigned long long* option_debug_buffer() { return g_dbg_buf; }
 
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args) {
@@ -132,6 +134,7 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
   if (!strcmp(name, "pdl")) slot = &g_opt_pdl;
   else if (!strcmp(name, "force_simt")) slot = &g_opt_force_simt;
   else if (!strcmp(name, "debug")) slot = &g_opt_debug;
+  else if (!strcmp(name, "tc")) slot = &g_opt_tc;
   if (!slot) {
     set_error("set_option: unknown option '%s'", name);
     return B200ATTN_EINVAL;

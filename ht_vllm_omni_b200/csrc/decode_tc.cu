@@ -1,0 +1,569 @@
+// decode_tc.cu — Kernel 2, tcgen05 flavour: persistent split-KV paged flash-decoding over an FP8 (e4m3) KV cache with
+// both GEMMs on the 5th-generation tensor cores (tcgen05.mma kind::f8f6f4, accumulators in TMEM) — no FP8->F16
+// conversion of K/V on the CUDA cores at all.
+//
+// Reference semantics are those of decode.cu (kernel_unified_attention, $VLLM/v1/attention/ops/triton_unified_attention.py:
+// 440-643, FlashInfer scale convention $VLLM/v1/attention/backends/flashinfer.py:1396-1404); the work plan, the partial
+// (o, m, l) workspace format and the in-kernel merge are shared with decode.cu, so both kernels are interchangeable
+// behind b200attn_decode.
+//
+// Per CTA (192 threads, 2 CTAs / SM):
+//   warp 4   producer: TMA tensor loads (UTMALDG, 128-B swizzle) of 16-token x 128-byte boxes out of the paged cache
+//            into two rings of 128-token tiles (K ring, V ring; 16 KiB per tile), bulk copy of the query rows.
+//   warp 5   MMA issuer (one lane): per 128-token tile
+//              S^T[128 tok x 16]  = K_tile[128 x 128 d] . Qop^T      4 x tcgen05.mma M128 N16 K32  (A, B K-major)
+//              O^T[128 d  x 16]  += V_tile^T[128 d x 128 tok] . P^T  <=4 x tcgen05.mma M128 N16 K32 (A, B MN-major)
+//            The K/V tiles are consumed exactly as TMA wrote them (the V tile is simply described MN-major).
+//   warps 0-3 softmax: thread = one token row of S^T (tcgen05.ld 32x32b), online softmax in the log2 domain against a
+//            CTA-wide lazily updated reference maximum, P written back to smem as e4m3 for the second GEMM.
+// FP8 operands without losing the 16-bit activations: the bf16 query is split EXACTLY into two e4m3 terms
+// q*2^k = hi + lo (8 significant bits = 4 + 4) that occupy N columns h and 8+h of the same MMA, and the probabilities are
+// split the same way (p*16 = hi + lo/16), so the column pairs are recombined in fp32 after the MMA.
+#include "decode_common.cuh"
+
+namespace b200attn {
+
+constexpr int kTcThreads = 192;
+constexpr int kTcTile = 128;                 // tokens per MMA tile (= 2 plan tiles of 64)
+constexpr int kTcStages = 3;                 // depth of the K ring and of the V ring
+constexpr int kTcTileBytes = kTcTile * kD;   // 16 KiB (fp8)
+constexpr int kTcBoxBytes = kChunkTokens * kD;
+constexpr int kTcQRawBytes = 8 * kD * 2;     // 8 query rows of 16-bit elements
+constexpr int kTcQopBytes = 16 * kD;         // 16 rows (8 hi + 8 lo) of e4m3
+constexpr int kTcPBytes = kTcTile * 16;      // [token][8 hi + 8 lo] e4m3
+constexpr int kTcScratchFloats = 160;
+constexpr int kTcTmemCols = 64;              // S0 [0,16) S1 [16,32) O [32,48)
+constexpr float kTcMargin = 4.0f;            // the reference maximum is raised when a logit exceeds it by 2^4
+constexpr float kTcPShift = 4.0f;            // p' = p * 2^4, so p' <= 2^8 < 448 (e4m3 max)
+
+struct TcSmem {
+  static constexpr int kK = 0;
+  static constexpr int kV = kK + kTcStages * kTcTileBytes;
+  static constexpr int kQRaw = kV + kTcStages * kTcTileBytes;
+  static constexpr int kQop = kQRaw + 2 * kTcQRawBytes;
+  static constexpr int kP = kQop + 2 * kTcQopBytes;
+  static constexpr int kScratch = kP + 2 * kTcPBytes;
+  static constexpr int kBars = kScratch + kTcScratchFloats * 4;
+  static constexpr int kNumBars = 4 * kTcStages + 16;
+  static constexpr int kTmemPtr = kBars + kNumBars * 8;
+  static constexpr int kTotal = kTmemPtr + 16 + 1024;  // + manual 1024-byte alignment
+  static_assert(kTotal <= 113 * 1024, "two CTAs per SM must fit");
+};
+
+// ---------------------------------------------------------------------------------------------
+// tcgen05 wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tc_mma_f8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrives (count 1) on an mbarrier of this CTA once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (SM100 "version 1"): start address, leading / stride byte offsets (all >> 4), layout.
+constexpr uint64_t kLayoutNone = 0, kLayoutSw128 = 2;
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint64_t layout) {
+  return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46) | (layout << 61);
+}
+// Instruction descriptor, kind::f8f6f4, e4m3 x e4m3 -> f32, M = 128, N = 16.
+constexpr uint32_t kIdescBase = (1u << 4) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
+constexpr uint32_t kIdescQK = kIdescBase;                              // A (K tile) K-major, B (Qop) K-major
+constexpr uint32_t kIdescPV = kIdescBase | (1u << 15) | (1u << 16);   // A (V tile) MN-major, B (P^T) MN-major
+
+__device__ __forceinline__ uint32_t f32x2_to_e4m3x2(float lo, float hi) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float2 e4m3x2_to_f32x2(uint32_t two_bytes) {
+  uint32_t h2;
+  asm("{\n\t.reg .b16 t;\n\tcvt.u16.u32 t, %1;\n\tcvt.rn.f16x2.e4m3x2 %0, t;\n\t}" : "=r"(h2) : "r"(two_bytes));
+  return __half22float2(*reinterpret_cast<__half2*>(&h2));
+}
+// x = hi + lo / lo_scale with hi, lo e4m3: returns the two bytes for a pair of values
+__device__ __forceinline__ void split_pair(float x0, float x1, float lo_scale, uint32_t& hi2, uint32_t& lo2) {
+  hi2 = f32x2_to_e4m3x2(x0, x1);
+  const float2 h = e4m3x2_to_f32x2(hi2);
+  lo2 = f32x2_to_e4m3x2((x0 - h.x) * lo_scale, (x1 - h.y) * lo_scale);
+}
+
+// ---------------------------------------------------------------------------------------------
+// The work of a CTA: its contiguous range of 64-token plan tiles, walked segment by segment ((sequence, kv head) runs)
+// and, inside a segment, MMA tile by MMA tile.  Every warp role walks the same sequence on its own.
+// ---------------------------------------------------------------------------------------------
+struct TcCursor {
+  int s, hv, tile, remaining;       // walk state (plan units)
+  int seg_s, seg_hv, seg_tile0, seg_n, seg_L, seg_end;
+  int u, m;                         // MMA tile index inside the segment, MMA tiles in the segment
+  int sg;                           // segment ordinal in this CTA
+  __device__ __forceinline__ void init(const int4& cs) { s = cs.x; hv = cs.y; tile = cs.z; remaining = cs.w; u = 0; m = 0; sg = -1; }
+  __device__ __forceinline__ bool next_segment(const DecodeParams& p) {
+    if (remaining <= 0 || s >= p.B) return false;
+    const int L = max(__ldg(p.seq_lens + s), 0);
+    const int nt = (L + kTileTokens - 1) / kTileTokens;
+    const int n = min(remaining, nt - tile);
+    seg_s = s; seg_hv = hv; seg_tile0 = tile; seg_n = n; seg_L = L;
+    seg_end = min((tile + n) * kTileTokens, L);
+    m = (n + 1) >> 1; u = -1; ++sg;
+    remaining -= n;
+    tile += n;
+    if (tile == nt) {
+      tile = 0;
+      if (++hv == p.Hv) {
+        hv = 0;
+        do { ++s; } while (s < p.B && remaining > 0 && __ldg(p.seq_lens + s) <= 0);
+      }
+    }
+    return true;
+  }
+  // advance to the next MMA tile; false when the CTA's range is exhausted
+  __device__ __forceinline__ bool next_tile(const DecodeParams& p) {
+    if (u + 1 < m) { ++u; return true; }
+    if (!next_segment(p)) return false;
+    u = 0;
+    return true;
+  }
+  __device__ __forceinline__ int tok0() const { return seg_tile0 * kTileTokens + u * kTcTile; }
+  __device__ __forceinline__ int valid() const { return min(kTcTile, seg_end - tok0()); }
+  __device__ __forceinline__ bool first() const { return u == 0; }
+  __device__ __forceinline__ bool last() const { return u == m - 1; }
+};
+
+template <int QDT>
+__global__ void __launch_bounds__(kTcThreads, 2)
+decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v, const DecodeParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));   // generic pointer to the aligned base
+  const uint32_t k_base = base + TcSmem::kK, v_base = base + TcSmem::kV;
+  const uint32_t qraw_base = base + TcSmem::kQRaw, qop_base = base + TcSmem::kQop, p_base = base + TcSmem::kP;
+  float* scratch = reinterpret_cast<float*>(gen + TcSmem::kScratch);
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(gen + TcSmem::kTmemPtr);
+  const uint32_t bar0 = base + TcSmem::kBars;
+  auto kfull = [&](uint32_t i) { return bar0 + i * 8; };
+  auto kempty = [&](uint32_t i) { return bar0 + (kTcStages + i) * 8; };
+  auto vfull = [&](uint32_t i) { return bar0 + (2 * kTcStages + i) * 8; };
+  auto vempty = [&](uint32_t i) { return bar0 + (3 * kTcStages + i) * 8; };
+  const uint32_t bar1 = bar0 + 4 * kTcStages * 8;
+  auto qfull = [&](uint32_t i) { return bar1 + i * 8; };
+  auto qempty = [&](uint32_t i) { return bar1 + (2 + i) * 8; };
+  auto qopfull = [&](uint32_t i) { return bar1 + (4 + i) * 8; };
+  auto qopempty = [&](uint32_t i) { return bar1 + (6 + i) * 8; };
+  auto sfull = [&](uint32_t i) { return bar1 + (8 + i) * 8; };
+  auto sempty = [&](uint32_t i) { return bar1 + (10 + i) * 8; };
+  auto pfull = [&](uint32_t i) { return bar1 + (12 + i) * 8; };
+  auto pempty = [&](uint32_t i) { return bar1 + (14 + i) * 8; };
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
+
+  // idle CTAs (fewer tiles than CTAs) leave before any TMEM allocation
+  const int4 cs = __ldg(reinterpret_cast<const int4*>(p.plan + kPlanHeaderWords) + blockIdx.x);
+  if (cs.x < 0 || cs.w <= 0) {
+    pdl_launch_dependents();
+    return;
+  }
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kTcStages; ++i) {
+      mbar_init(kfull(i), 1); mbar_init(kempty(i), 1);
+      mbar_init(vfull(i), 1); mbar_init(vempty(i), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(qfull(i), 1); mbar_init(qempty(i), 4);
+      mbar_init(qopfull(i), 4); mbar_init(qopempty(i), 1);
+      mbar_init(sfull(i), 1); mbar_init(sempty(i), 4);
+      mbar_init(pfull(i), 4); mbar_init(pempty(i), 1);
+    }
+    mbar_fence_init();
+    prefetch_tensormap(&tm_k);
+    prefetch_tensormap(&tm_v);
+  }
+  if (warp == 5) {  // TMEM: one warp allocates (and frees at the end)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + TcSmem::kTmemPtr), "r"(kTcTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) dbg_stamp(p, 1);
+
+  if (warp == 4) {
+    // =========================================== producer ===========================================
+    const uint64_t pol = policy_evict_first();
+    TcCursor cur; cur.init(cs);
+    const uint16_t* qptr = reinterpret_cast<const uint16_t*>(p.q);
+    bool waited = false, q_issued = true;
+    int early_left = p.fresh >= 0 ? kTcStages : 0;
+    uint32_t it = 0;       // MMA tile ordinal in this CTA
+    int blk = 0;
+    const int32_t* bt = nullptr;
+    int kvh = 0;
+    auto issue_q = [&]() {
+      const uint32_t slot = cur.sg & 1;
+      mbar_wait(qempty(slot), ((cur.sg >> 1) & 1) ^ 1);
+      if (lane == 0) mbar_arrive_expect_tx(qfull(slot), (uint32_t)p.G * kD * 2);
+      __syncwarp();
+      if (lane < p.G) {
+        const uint16_t* src = qptr + (int64_t)cur.seg_s * p.q_stride_t + (int64_t)(cur.seg_hv * p.G + lane) * p.q_stride_h;
+        bulk_load_1d(qraw_base + slot * kTcQRawBytes + lane * (kD * 2), src, kD * 2, qfull(slot));
+      }
+      q_issued = true;
+    };
+    while (cur.next_tile(p)) {
+      if (cur.first()) {
+        q_issued = false;
+        const int row = p.row_map ? __ldg(p.row_map + cur.seg_s) : cur.seg_s;
+        bt = p.block_table + (int64_t)row * p.bt_stride;
+        kvh = cur.seg_hv / p.gsplit;
+      }
+      const int tok0 = cur.tok0();
+      // a segment's query rows must be requested before we move past the segment: early tiles only while more tiles of
+      // the same segment follow, so the request below always happens with this segment's cursor
+      const bool early_ok = !waited && early_left > 0 && !cur.last() && tok0 + kTcTile <= cur.seg_L - p.fresh;
+      if (!early_ok && !waited) { pdl_wait(); waited = true; }
+      if (waited && !q_issued) issue_q();
+      if (early_ok) --early_left;
+      if ((cur.u & 3) == 0) {  // 32 box -> block ids (4 MMA tiles) with one coalesced load
+        const int ci = (tok0 >> 4) + lane;
+        blk = (ci * kChunkTokens < cur.seg_L) ? __ldg(bt + ci / p.cpb) : 0;
+      }
+      const int nbox = (cur.valid() + kChunkTokens - 1) / kChunkTokens;
+      const uint32_t st = it % kTcStages, par = ((it / kTcStages) & 1) ^ 1;
+      const int c = lane & 7;
+      const int b = __shfl_sync(0xffffffffu, blk, ((cur.u & 3) << 3) + c);
+      const int ci = (tok0 >> 4) + c;
+      const int row0 = (ci % p.cpb) * kChunkTokens;
+      mbar_wait(kempty(st), par);
+      if (lane == 0) mbar_arrive_expect_tx(kfull(st), (uint32_t)nbox * kTcBoxBytes);
+      __syncwarp();
+      if (lane < 8 && c < nbox) tma_load_4d(k_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_k, kfull(st), 0, row0, kvh, b, pol);
+      mbar_wait(vempty(st), par);
+      if (lane == 0) mbar_arrive_expect_tx(vfull(st), (uint32_t)nbox * kTcBoxBytes);
+      __syncwarp();
+      if (lane >= 8 && lane < 16 && c < nbox) tma_load_4d(v_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_v, vfull(st), 0, row0, kvh, b, pol);
+      if (it == 0 && lane == 0) dbg_stamp(p, 2);
+      ++it;
+    }
+    if (!waited) pdl_wait();
+  } else if (warp == 5) {
+    // =========================================== MMA issuer ===========================================
+    pdl_wait();
+    TcCursor cq, cp;
+    cq.init(cs); cp.init(cs);
+    uint32_t iq = 0, ip = 0;  // tile ordinals of the QK and PV streams
+    auto issue_qk = [&]() {
+      const uint32_t slot = cq.sg & 1, b = iq & 1, st = iq % kTcStages;
+      if (cq.first()) mbar_wait(qopfull(slot), (cq.sg >> 1) & 1);
+      mbar_wait(kfull(st), (iq / kTcStages) & 1);
+      mbar_wait(sempty(b), ((iq >> 1) & 1) ^ 1);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = tc_desc(k_base + st * kTcTileBytes + k * 32, 16, 1024, kLayoutSw128);
+          const uint64_t db = tc_desc(qop_base + slot * kTcQopBytes + k * 256, 128, 1024, kLayoutNone);
+          tc_mma_f8(tmem + b * 16, da, db, kIdescQK, k > 0);
+        }
+        tc_commit(kempty(st));
+        tc_commit(sfull(b));
+        if (cq.last()) tc_commit(qopempty(slot));
+      }
+      __syncwarp();
+      ++iq;
+    };
+    auto issue_pv = [&]() {
+      const uint32_t b = ip & 1, st = ip % kTcStages;
+      mbar_wait(vfull(st), (ip / kTcStages) & 1);
+      mbar_wait(pfull(b), (ip >> 1) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const int nk = (cp.valid() + 31) >> 5;
+        for (int k = 0; k < nk; ++k) {
+          const uint64_t da = tc_desc(v_base + st * kTcTileBytes + k * 4096, 0, 1024, kLayoutSw128);
+          const uint64_t db = tc_desc(p_base + b * kTcPBytes + k * 512, 128, 0, kLayoutNone);
+          tc_mma_f8(tmem + 32, da, db, kIdescPV, (k > 0 || !cp.first()) ? 1u : 0u);
+        }
+        tc_commit(vempty(st));
+        tc_commit(pempty(b));
+      }
+      __syncwarp();
+      ++ip;
+    };
+    if (cq.next_tile(p)) issue_qk();
+    while (cp.next_tile(p)) {
+      // QK of the next tile runs while the softmax warps work on this one -- inside a segment.  Across a segment boundary
+      // the order flips: the next segment's Qop is only written after the softmax warps have seen this segment's last PV.
+      const bool have = cq.next_tile(p);
+      if (have && !cq.first()) issue_qk();
+      issue_pv();
+      if (have && cq.first()) issue_qk();
+    }
+  } else {
+    // =========================================== softmax warps ===========================================
+    pdl_wait();
+    const int w = warp;
+    const int tid = threadIdx.x;  // 0..127 = row of the 128-row MMA tiles (token for S^T, head dim for O^T)
+    const uint32_t lane_base = (uint32_t)(w * 32) << 16;   // TMEM lanes this warp may touch
+    float* cs_sm = scratch;                                  // [2][8]  logit scale per head (by Q slot)
+    float* wmax = scratch + 16;                              // [4][8]  per-warp tile maxima
+    volatile int* flags = reinterpret_cast<volatile int*>(scratch + 48);  // [2][4] "a logit left the window" votes
+    float* red_l = scratch + 56;                             // [4][8]  per-warp row sums
+    float* red_o = scratch + 88;                             // merge scratch (32 floats)
+    float* red_ml = scratch + 120;                           // merge scratch (16 floats)
+    volatile int* hand = reinterpret_cast<volatile int*>(scratch + 136);
+    const float ninf = -INFINITY;
+    TcCursor cur; cur.init(cs);
+    uint32_t it = 0;
+    float m_ref[8], l_part[8], crow[8];
+    bool stamped = false;
+
+    while (cur.next_tile(p)) {
+      if (cur.first()) {
+        // ---------------- new segment: split the 16-bit query rows into e4m3 hi / lo operand rows ----------------
+        const uint32_t slot = cur.sg & 1;
+        const int kvh = cur.seg_hv / p.gsplit;
+        mbar_wait(qfull(slot), (cur.sg >> 1) & 1);
+        const int h = tid >> 4, part = tid & 15;   // 16 threads per head, 8 consecutive head dims each
+        uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+        if (h < p.G) raw = lds128(qraw_base + slot * kTcQRawBytes + h * (kD * 2) + part * 16);
+        float f[8];
+        f[0] = q_to_float<QDT>(raw.x & 0xffff); f[1] = q_to_float<QDT>(raw.x >> 16);
+        f[2] = q_to_float<QDT>(raw.y & 0xffff); f[3] = q_to_float<QDT>(raw.y >> 16);
+        f[4] = q_to_float<QDT>(raw.z & 0xffff); f[5] = q_to_float<QDT>(raw.z >> 16);
+        f[6] = q_to_float<QDT>(raw.w & 0xffff); f[7] = q_to_float<QDT>(raw.w >> 16);
+        float amax = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(f[i]));
+#pragma unroll
+        for (int off = 1; off < 16; off <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+        // exact power-of-two pre-scale that puts the row maximum in [128, 256); undone on the logits
+        const uint32_t eb = (__float_as_uint(amax) >> 23) & 0xffu;
+        const bool norm = eb >= 16 && eb < 255;
+        const float inv = norm ? __uint_as_float((261u - eb) << 23) : 1.0f;
+        const float fct = norm ? __uint_as_float((eb - 7u) << 23) : 1.0f;
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split_pair(f[2 * i] * inv, f[2 * i + 1] * inv, 16.0f, hi[i], lo[i]);
+        mbar_wait(qopempty(slot), ((cur.sg >> 1) & 1) ^ 1);   // the MMAs of segment sg-2 are done with this slot
+        // K-major, no swizzle: 8x16-byte core matrices; byte (row r, d) at (r/8)*1024 + (d/16)*128 + (r%8)*16 + d%16
+        const uint32_t qa = qop_base + slot * kTcQopBytes + (part >> 1) * 128 + h * 16 + (part & 1) * 8;
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(hi[0] | (hi[1] << 16)), "r"(hi[2] | (hi[3] << 16)) : "memory");
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa + 1024), "r"(lo[0] | (lo[1] << 16)), "r"(lo[2] | (lo[3] << 16)) : "memory");
+        if (part == 0) {
+          const float kscale = __ldg(p.k_scale + (int64_t)kvh * p.scale_stride);
+          cs_sm[slot * 8 + h] = (h < p.G) ? fct * p.sm_scale_log2 * kscale : 0.f;
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (lane == 0) {
+          mbar_arrive(qopfull(slot));
+          mbar_arrive(qempty(slot));
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          crow[i] = cs_sm[slot * 8 + i];
+          m_ref[i] = ninf;
+          l_part[i] = 0.f;
+        }
+      }
+
+      // ---------------- one 128-token tile: S^T row of this thread's token ----------------
+      const uint32_t b = it & 1;
+      mbar_wait(sfull(b), (it >> 1) & 1);
+      tc_fence_after();
+      if (!stamped && tid == 0) { dbg_stamp(p, 3); stamped = true; }
+      uint32_t r[16];
+      tc_ld16(tmem + lane_base + b * 16, r);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sempty(b));
+      const bool ok = cur.tok0() + tid < cur.seg_end;
+      float x[8];
+      bool exceed = false;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        x[i] = ok ? (__uint_as_float(r[i]) + __uint_as_float(r[8 + i]) * 0.0625f) * crow[i] : ninf;
+        exceed |= x[i] > m_ref[i] + kTcMargin;
+      }
+      const int any = __any_sync(0xffffffffu, exceed);
+      if (lane == 0) flags[b * 4 + w] = any;
+      named_bar_sync(1, 128);
+      if (flags[b * 4 + 0] | flags[b * 4 + 1] | flags[b * 4 + 2] | flags[b * 4 + 3]) {
+        // ---------------- raise the CTA-wide reference maximum (always on a segment's first tile, rare later) ----------------
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float mx = x[i];
+#pragma unroll
+          for (int off = 1; off < 32; off <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+          if (lane == 0) wmax[w * 8 + i] = mx;
+        }
+        named_bar_sync(1, 128);
+        float fac[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float t = fmaxf(fmaxf(wmax[i], wmax[8 + i]), fmaxf(wmax[16 + i], wmax[24 + i]));
+          const float mn = fmaxf(m_ref[i], t);
+          fac[i] = (m_ref[i] == ninf) ? 0.f : fast_exp2(m_ref[i] - mn);
+          m_ref[i] = mn;
+          l_part[i] *= fac[i];
+        }
+        if (!cur.first()) {
+          // O^T lives in TMEM: wait for every PV issued so far, then scale this thread's row (head dim) of it
+          mbar_wait(pempty((it - 1) & 1), ((it - 1) >> 1) & 1);
+          tc_fence_after();
+          uint32_t o[16];
+          tc_ld16(tmem + lane_base + 32, o);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            o[i] = __float_as_uint(__uint_as_float(o[i]) * fac[i]);
+            o[8 + i] = __float_as_uint(__uint_as_float(o[8 + i]) * fac[i]);
+          }
+          tc_st16(tmem + lane_base + 32, o);
+          tc_fence_before();
+        }
+      }
+      // p' = 2^(x - m_ref + 4) in (0, 256], split into e4m3 hi + lo/16
+      float pr[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        pr[i] = fast_exp2(x[i] - m_ref[i] + kTcPShift);
+        l_part[i] += pr[i];
+      }
+      uint32_t ph[4], pl[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) split_pair(pr[2 * i], pr[2 * i + 1], 16.0f, ph[i], pl[i]);
+      mbar_wait(pempty(b), ((it >> 1) & 1) ^ 1);   // PV of tile it-2 no longer reads this P buffer
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(p_base + b * kTcPBytes + tid * 16), "r"(ph[0] | (ph[1] << 16)),
+                   "r"(ph[2] | (ph[3] << 16)), "r"(pl[0] | (pl[1] << 16)), "r"(pl[2] | (pl[3] << 16))
+                   : "memory");
+      {
+        // rows of the V tile past the valid count that the last 32-token MMA step still reads: stale smem or cache slots
+        // beyond seq_len (possibly NaN patterns) must not meet p = 0
+        const int v = cur.valid();
+        if (v & 31) {
+          const uint32_t st = it % kTcStages;
+          mbar_wait(vfull(st), (it / kTcStages) & 1);
+          const int nchunk = (32 - (v & 31)) * 8;
+          for (int idx = tid; idx < nchunk; idx += 128)
+            asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(v_base + st * kTcTileBytes + (v + (idx >> 3)) * 128 + (idx & 7) * 16), "r"(0u) : "memory");
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pfull(b));
+      ++it;
+
+      if (cur.last()) {
+        // ---------------- segment end: O^T row of this thread's head dim, row sums, output or partial ----------------
+        if (tid == 0 && cur.remaining <= 0) dbg_stamp(p, 4);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float v = l_part[i];
+#pragma unroll
+          for (int off = 1; off < 32; off <<= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+          if (lane == 0) red_l[w * 8 + i] = v;
+        }
+        mbar_wait(pempty((it - 1) & 1), ((it - 1) >> 1) & 1);   // the segment's last PV has completed
+        tc_fence_after();
+        uint32_t o[16];
+        tc_ld16(tmem + lane_base + 32, o);
+        tc_fence_before();
+        named_bar_sync(1, 128);
+        const int s = cur.seg_s, hv = cur.seg_hv, L = cur.seg_L;
+        const int kvh = hv / p.gsplit;
+        const bool whole = (cur.seg_tile0 == 0) && ((cur.seg_tile0 + cur.seg_n) * kTileTokens >= L);
+        const float vscale = __ldg(p.v_scale + (int64_t)kvh * p.scale_stride);
+        const int pslot = cur.sg == 0 ? 0 : 1;
+        const int d = tid;
+        using E = Elem<QDT>;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (i < p.G) {
+            const float lg = (red_l[i] + red_l[8 + i]) + (red_l[16 + i] + red_l[24 + i]);
+            const float acc = __uint_as_float(o[i]) + __uint_as_float(o[8 + i]) * 0.0625f;
+            const float mg = m_ref[i] - kTcPShift;   // p' = 2^(x - mg)
+            if (whole) {
+              const int hq = hv * p.G + i;
+              typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+              op[d] = E::from_float(acc * (vscale / lg));
+              if (p.lse_out != nullptr && d == 0) p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
+            } else {
+              const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + i;
+              __stcg(p.ws_o + pidx * kD + d, acc);
+              if (d == 0) __stcg(reinterpret_cast<float2*>(p.ws_ml + pidx * 2), make_float2(mg, lg));
+            }
+          }
+        }
+        if (!whole && p.fused_merge) {
+          const int pfx = __ldg(p.plan + kPlanPrefixOffset + s);
+          fused_merge_tail<QDT, 8>(p, s, hv, L, pfx, vscale, tid, red_o, red_ml, hand);
+        }
+        named_bar_sync(1, 128);
+      }
+    }
+    if (tid == 0) dbg_stamp(p, 5);
+  }
+
+  // teardown: every role is done with TMEM (the softmax warps waited for the last PV)
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTcTmemCols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
+
+template <int QDT>
+static int launch_tc(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, cudaStream_t stream) {
+  auto fn = decode_tc_kernel<QDT>;
+  static bool configured = false;
+  if (!configured) {
+    if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem::kTotal), "cudaFuncSetAttribute(decode_tc smem)"))
+      return B200ATTN_ECUDA;
+    configured = true;
+  }
+  void* args[] = {(void*)&tk, (void*)&tv, (void*)&p};
+  return launch_with_pdl((const void*)fn, dim3(grid), dim3(kTcThreads), TcSmem::kTotal, stream, args);
+}
+
+// fp8 KV, group size <= 8 per (virtual) kv head
+int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, int q_dtype, cudaStream_t stream) {
+  return q_dtype == B200ATTN_BF16 ? launch_tc<B200ATTN_BF16>(tk, tv, p, grid, stream) : launch_tc<B200ATTN_FP16>(tk, tv, p, grid, stream);
+}
+
+}  // namespace b200attn

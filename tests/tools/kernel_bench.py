@@ -21,7 +21,7 @@ def main():
     ap.add_argument("--Hq", type=int, default=16); ap.add_argument("--Hkv", type=int, default=2)
     ap.add_argument("--kv", default="fp8"); ap.add_argument("--layers", type=int, default=8)
     ap.add_argument("--ctas", default="0"); ap.add_argument("--debug", default="0"); ap.add_argument("--pdl", type=int, default=0)
-    ap.add_argument("--graph", type=int, default=0); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--ragged", type=int, default=0)
+    ap.add_argument("--tc", type=int, default=1); ap.add_argument("--graph", type=int, default=0); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--ragged", type=int, default=0)
     a = ap.parse_args()
     dev = torch.device("cuda")
     lib = ops.load_library()
@@ -48,6 +48,7 @@ def main():
     slots = (bt.to(torch.int64)[torch.arange(B), torch.from_numpy((lens - 1) // bs).to(dev)] * bs + torch.from_numpy((lens - 1) % bs).to(dev)).contiguous()
     dec_b, wr_b = algorithmic_bytes(lens, Hq, Hkv, D, bs, 1 if fp8 else 2)
     lib.b200attn_set_option(b"pdl", a.pdl)
+    lib.b200attn_set_option(b"tc", a.tc)
     for ctas in [int(x) for x in a.ctas.split(",")]:
         for dbg in [int(x) for x in a.debug.split(",")]:
             lib.b200attn_set_option(b"debug", dbg)
@@ -107,7 +108,7 @@ def main():
                     print(f"  graph/layer pdl={pdl}: decode {t_d:.2f} | decode+merge {t_dm:.2f} | write+decode+merge {t_wdm:.2f} | write only {t_w:.2f} | merge only {t_m:.2f} us"
                           f"  => decode {dec_b / t_d / 1e3:.0f} GB/s, all {(dec_b + wr_b) / t_wdm / 1e3:.0f} GB/s", flush=True)
                 lib.b200attn_set_option(b"pdl", a.pdl)
-            print(f"B={B} L={L} ({Hq},{Hkv}) {a.kv} ctas={ws.num_ctas} debug={dbg} pdl={a.pdl} | decode mean {td[0]:.2f} med {td[1]:.2f} min {td[2]:.2f} us "
+            print(f"B={B} L={L} ({Hq},{Hkv}) {a.kv} tc={a.tc} ctas={ws.num_ctas} debug={dbg} pdl={a.pdl} | decode mean {td[0]:.2f} med {td[1]:.2f} min {td[2]:.2f} us "
                   f"= {dec_b / td[1] / 1e3:.0f} GB/s | merge {tm[1]:.2f} us | kv_write {tw[1]:.2f} us | write+decode+merge {tall[1]:.2f} us", flush=True)
     lib.b200attn_set_option(b"debug", 0)
 

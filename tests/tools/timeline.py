@@ -16,6 +16,7 @@ ks = torch.full((Hkv,), 0.01, device=dev); vs = torch.full((Hkv,), 0.01, device=
 ws = ops.DecodeWorkspace(dev, B, torch.uint8); ws.make_plan(lens, Hq, Hkv)
 buf = torch.zeros(ws.num_ctas * 8, dtype=torch.int64, device=dev)
 lib.b200attn_set_option(b"pdl", 0)
+lib.b200attn_set_option(b"tc", int(os.environ.get("B200_TC", "1")))
 fn = lib.b200attn_debug_set_timeline_buffer; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
 for dbg in (0, 1):
     lib.b200attn_set_option(b"debug", dbg)
