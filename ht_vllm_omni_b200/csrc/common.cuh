@@ -26,13 +26,13 @@ static_assert(kTileTokens == B200ATTN_TILE_TOKENS, "header / kernel tile mismatc
 // Plan buffer layout (int32 words):
 //   [0] total_tiles  [1] tiles_per_cta  [2] grid  [3] num_seqs  [4] num_kv_heads (virtual)  [5..7] 0
 //   [8 .. 8+kMaxGrid*4)         int4 cta_start[kMaxGrid] = {seq, kv_head, tile, n_tiles}  (seq=-1: idle)
-//   [.. +kMaxGrid*2)            arrival counters of the in-kernel merge, one per (first CTA, slot) of a split
-//                               (sequence, kv head) pair; zeroed by the plan kernel, self-resetting afterwards
+//   [.. +kMaxGrid*4)            counters of the in-kernel merge, one (ticket, published) pair per (first CTA, slot) of a
+//                               split (sequence, kv head) pair; zeroed by the plan kernel, self-resetting afterwards
 //   [.. +B+1)                   tile_prefix[num_seqs+1] (exclusive scan of ceil(L/64))
 constexpr int kPlanHeaderWords = 8;
 constexpr int kPlanCtaWords = kMaxGrid * 4;
 constexpr int kPlanCounterOffset = kPlanHeaderWords + kPlanCtaWords;
-constexpr int kPlanCounterWords = kMaxGrid * 2;
+constexpr int kPlanCounterWords = kMaxGrid * 4;   // [0, 2*kMaxGrid): arrival tickets, [2*kMaxGrid, 4*kMaxGrid): published partials
 constexpr int kPlanPrefixOffset = kPlanCounterOffset + kPlanCounterWords;
 
 // Workspace layout: ws_o [grid][2 slots][16 heads][D] fp32, then ws_ml [grid][2][16][2] fp32.

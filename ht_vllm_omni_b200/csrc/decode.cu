@@ -478,7 +478,10 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     {
       const int pslot = sg == 0 ? 0 : 1;
       const int d = tid;  // 128 consumer threads <-> 128 head dims
-      for (int head = 0; head < p.G; ++head) {
+      constexpr int GH = NT * 8;
+      float accv[GH], mgv[GH], lgv[GH];
+#pragma unroll
+      for (int head = 0; head < GH; ++head) {
         float mg = ninf;
 #pragma unroll
         for (int ww = 0; ww < kConsumerWarps; ++ww) mg = fmaxf(mg, red_ml[(ww * kMaxGroup + head) * 2]);
@@ -489,23 +492,28 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
           lg += (mw == ninf) ? 0.f : red_ml[(ww * kMaxGroup + head) * 2 + 1] * fast_exp2(mw - mg);
           acc += red_o[((ww * NT * 8) + head) * kRedStride + d];
         }
-        if (whole) {
-          const int hq = hv * p.G + head;
-          using E = Elem<QDT>;
-          typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
-          op[d] = E::from_float(acc * (vscale / lg));
-          if (p.lse_out != nullptr && d == 0)
-            p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
-        } else {
-          const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + head;
-          __stcg(p.ws_o + pidx * kD + d, acc);
-          if (d == 0) __stcg(reinterpret_cast<float2*>(p.ws_ml + pidx * 2), make_float2(mg, lg));
+        accv[head] = acc; mgv[head] = mg; lgv[head] = lg;
+        if (head < p.G) {
+          if (whole) {
+            const int hq = hv * p.G + head;
+            using E = Elem<QDT>;
+            typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+            op[d] = E::from_float(acc * (vscale / lg));
+            if (p.lse_out != nullptr && d == 0)
+              p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
+          } else if (!p.fused_merge) {
+            const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + head;
+            __stcg(p.ws_o + pidx * kD + d, acc);
+            if (d == 0) __stcg(reinterpret_cast<float2*>(p.ws_ml + pidx * 2), make_float2(mg, lg));
+          }
         }
       }
-    }
-    // ---------------- in-kernel merge: the last CTA to deliver a partial of this (sequence, kv head) pair reduces them ----------------
-    if (!whole && p.fused_merge) {
-      fused_merge_tail<QDT, NT * 8>(p, s, hv, L, pfx, vscale, tid, red_o, red_ml, desc + 16);
+      // in-kernel merge: the last CTA to finish a piece of this (sequence, kv head) pair reduces all of them
+      if (!whole && p.fused_merge) {
+        MergeTicket tk = {};
+        if (tid == 0) tk = merge_draw_ticket(p, hv, L, pfx);
+        fused_merge_tail<QDT, GH, false>(p, s, hv, vscale, tid, pslot, tk, accv, mgv, lgv, red_o, desc + 16, nullptr);
+      }
     }
     named_bar_sync(1, kConsumerWarps * 32);
     remaining -= n;

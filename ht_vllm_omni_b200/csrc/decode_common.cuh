@@ -48,125 +48,156 @@ __device__ __forceinline__ float q_to_float(uint16_t raw) {
   else return __half2float(__ushort_as_half(raw));
 }
 
-// In-kernel merge (reduce_segments semantics, $VLLM/v1/attention/ops/triton_unified_attention.py:645-733): called by the
-// 128 epilogue threads of a CTA right after they stored a partial (o, m, l) of the pair (s, hv) to the workspace.  The
-// last CTA to deliver a partial of the pair reduces all of them and writes `out`.  GH = heads held per thread (8 or 16),
-// red_o / red_ml = smem scratch of >= GH*4 and >= 2*GH floats, hand = 3 ints of smem.
-template <int QDT, int GH>
-__device__ __forceinline__ void fused_merge_tail(const DecodeParams& p, int s, int hv, int L, int pfx, float vscale, int tid,
-                                                 float* red_o, float* red_ml, volatile int* hand) {
+// In-kernel merge (reduce_segments semantics, $VLLM/v1/attention/ops/triton_unified_attention.py:645-733) of the split-KV
+// partials of one (sequence, virtual kv head) pair.  Called by the 128 epilogue threads of a CTA at the end of a segment that
+// does not cover its whole sequence; thread `tid` holds, for head dim d = tid and every head h < G, the CTA's unnormalised
+// partial acc[h] = sum_j 2^(x_j - mg[h]) v_j[d] together with (mg[h], lg[h]).
+//   1. one thread draws a ticket from the pair's arrival counter;
+//   2. every CTA but the last stores its partial to the workspace and bumps the pair's "published" counter with a release;
+//   3. the last CTA never stores its own partial: it waits until the others are published (normally long ago), loads their
+//      partials (one L2 round trip, all loads in flight at once) and combines them with its registers.
+// Both counters live in the plan buffer (zeroed by the plan kernel, re-armed here by the last CTA).  mrg = smem scratch of
+// 64 floats, hand = 3 ints of smem.
+// Ticket of the in-kernel merge (one thread): where the pair's counters are and in which order this CTA arrived.
+struct MergeTicket {
+  int* cnt;       // arrival counter; the "published" counter sits kPlanCounterWords / 2 words further
+  int ticket, np, c_lo, slot_lo;
+};
+__device__ __forceinline__ MergeTicket merge_draw_ticket(const DecodeParams& p, int hv, int L, int pfx) {
+  MergeTicket t;
+  const int tpc = __ldg(p.plan + 1);
+  const int nt = (L + kTileTokens - 1) / kTileTokens;
+  const long long x0 = (long long)pfx * p.Hv + (long long)hv * nt;
+  t.c_lo = (int)(x0 / tpc);
+  const int c_hi = (int)((x0 + nt - 1) / tpc);
+  t.slot_lo = (x0 == (long long)t.c_lo * tpc) ? 0 : 1;
+  t.cnt = p.plan + kPlanCounterOffset + t.c_lo * 2 + t.slot_lo;
+  t.np = c_hi - t.c_lo + 1;
+  t.ticket = atomicAdd(t.cnt, 1);
+  return t;
+}
+// release: every store this thread has observed (its own, and through barriers the other epilogue threads') is visible
+// to whoever acquires the bumped counter
+__device__ __forceinline__ void merge_publish(int* pub) {
+  asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(pub) : "memory");
+}
+
+// Request ring between the epilogue threads and the publish-helper warp (smem): ring[0] = number of requests pushed so far
+// (low 32 bits), ring[1 + (i & 7)] = request i (address of a "published" counter, or 0 = "no more requests").  A CTA cuts at
+// most two (sequence, kv head) pairs, so at most three requests are ever pushed and the ring cannot overflow.
+__device__ __forceinline__ void pub_ring_push(volatile unsigned long long* ring, unsigned long long req) {
+  const uint32_t n = (uint32_t)ring[0];
+  ring[1 + (n & 7)] = req;
+  const uint32_t a = smem_u32(const_cast<unsigned long long*>(ring));
+  asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(a), "r"(n + 1) : "memory");
+}
+__device__ __forceinline__ uint32_t pub_ring_count(volatile unsigned long long* ring) {
+  uint32_t n;
+  asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(n) : "r"(smem_u32(const_cast<unsigned long long*>(ring))) : "memory");
+  return n;
+}
+
+// `tk` is thread 0's ticket (drawn any time before; other threads pass anything).  kAsyncPublish: instead of fencing inline
+// (one memory round trip, several microseconds while the CTA's own KV stream saturates HBM), thread 0 leaves the address of
+// the "published" counter in the request ring `pub_req`; a helper warp polls the ring and does the release + signal.
+template <int QDT, int GH, bool kAsyncPublish>
+__device__ __forceinline__ void fused_merge_tail(const DecodeParams& p, int s, int hv, float vscale, int tid, int pslot,
+                                                 const MergeTicket& tk, const float (&acc)[GH], const float (&mg)[GH],
+                                                 const float (&lg)[GH], float* mrg, volatile int* hand,
+                                                 volatile unsigned long long* pub_req) {
   const float ninf = -INFINITY;
-  {
-      named_bar_sync(1, kConsumerWarps * 32);  // all partial stores of this CTA are issued ...
-      if (tid == 0) {
-        const int tpc = __ldg(p.plan + 1);
-        const int nt = (L + kTileTokens - 1) / kTileTokens;
-        const long long x0 = (long long)pfx * p.Hv + (long long)hv * nt;
-        const int c_lo = (int)(x0 / tpc), c_hi = (int)((x0 + nt - 1) / tpc);
-        const int slot_lo = (x0 == (long long)c_lo * tpc) ? 0 : 1;
-        int* cnt = p.plan + kPlanCounterOffset + c_lo * 2 + slot_lo;
-        const int np = c_hi - c_lo + 1;
-        __threadfence();  // ... and (cumulatively, through the barrier) made visible device-wide before the arrival counts
-        const int old = atomicAdd(cnt, 1);
-        const bool last = (old == np - 1);
-        if (last) {
-          *cnt = 0;         // every partial of the pair has arrived: re-arm the counter for the next launch
-          __threadfence();  // acquire side of the hand-shake
-        }
-        hand[0] = last ? np : 0;
-        hand[1] = c_lo;
-        hand[2] = slot_lo;
+  if (tid == 0) {
+    hand[0] = (tk.ticket == tk.np - 1) ? tk.np : 0;
+    hand[1] = tk.c_lo;
+    hand[2] = tk.slot_lo;
+  }
+  named_bar_sync(1, kConsumerWarps * 32);
+  const int np = hand[0], c_lo = hand[1], slot_lo = hand[2];
+  if (np == 0) {
+    // ---- not the last: publish the partial ----
+#pragma unroll
+    for (int h = 0; h < GH; ++h) {
+      if (h < p.G) {
+        const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + h;
+        __stcg(p.ws_o + pidx * kD + tid, acc[h]);
+        if (tid == 0) __stcg(reinterpret_cast<float2*>(p.ws_ml + pidx * 2), make_float2(mg[h], lg[h]));
       }
-      named_bar_sync(1, kConsumerWarps * 32);
-      const int np = hand[0];
-      if (np > 0) {
-        const int c_lo = hand[1], slot_lo = hand[2];
-        auto part = [&](int i, int head) { return ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head; };
-        constexpr int CH = GH == 8 ? 4 : 2;   // partials merged per round with every load in flight at once
-        const int d = tid;
-        using E = Elem<QDT>;
-        if (np <= CH) {
-          // fast path (the common case: a pair cut by one to three CTA boundaries).  One round trip to L2: issue the
-          // partial-output loads first, then the (m, l) loads, then combine.
-          float ov[CH][GH];
-#pragma unroll
-          for (int i = 0; i < CH; ++i)
-#pragma unroll
-            for (int h = 0; h < GH; ++h) ov[i][h] = (i < np && h < p.G) ? ldcg_f32(p.ws_o + part(i, h) * kD + d) : 0.f;
-          {
-            const int head = tid >> 3, i = tid & 7;   // 8 lanes per head, lane i <-> partial i
-            float2 ml = make_float2(ninf, 0.f);
-            if (head < p.G && i < np) ml = ldcg_f32x2(p.ws_ml + part(i, head) * 2);
-            float mg = ml.x;
-#pragma unroll
-            for (int off = 1; off < 8; off <<= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
-            const float wgt = (ml.x == ninf) ? 0.f : fast_exp2(ml.x - mg);
-            float lg = ml.y * wgt;
-#pragma unroll
-            for (int off = 1; off < 8; off <<= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
-            if (head < p.G && i < CH) red_o[head * CH + i] = wgt * (vscale / lg);   // normalised weight of partial i
-            if (head < p.G && i == 0) red_ml[head] = (mg + fast_log2(lg)) * 0.6931471805599453f;
-          }
-          named_bar_sync(1, kConsumerWarps * 32);
-#pragma unroll
-          for (int h = 0; h < GH; ++h) {
-            if (h < p.G) {
-              float acc = 0.f;
-#pragma unroll
-              for (int i = 0; i < CH; ++i) acc += red_o[h * CH + i] * ov[i][h];   // weights of absent partials are 0
-              const int hq = hv * p.G + h;
-              typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
-              op[d] = E::from_float(acc);
-              if (p.lse_out != nullptr && d == 0) p.lse_out[(int64_t)s * p.Hq + hq] = red_ml[h];
-            }
-          }
-        } else {
-          // general path: any number of partials (small batches with very long contexts)
-          {
-            const int head = tid >> 3, sub = tid & 7;
-            float mg = ninf, lg = 0.f;
-            if (head < p.G)
-              for (int i = sub; i < np; i += 8) mg = fmaxf(mg, ldcg_f32(p.ws_ml + part(i, head) * 2));
-#pragma unroll
-            for (int off = 1; off < 8; off <<= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
-            if (head < p.G)
-              for (int i = sub; i < np; i += 8) {
-                const float2 ml = ldcg_f32x2(p.ws_ml + part(i, head) * 2);
-                lg += (ml.x == ninf) ? 0.f : ml.y * fast_exp2(ml.x - mg);
-              }
-#pragma unroll
-            for (int off = 1; off < 8; off <<= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
-            if (sub == 0 && head < p.G) {
-              red_ml[head * 2 + 0] = mg;
-              red_ml[head * 2 + 1] = lg;
-            }
-          }
-          named_bar_sync(1, kConsumerWarps * 32);
-          float acc[GH];
-#pragma unroll
-          for (int h = 0; h < GH; ++h) acc[h] = 0.f;
-          for (int i = 0; i < np; ++i) {
-            float ov[GH], mv[GH];
-#pragma unroll
-            for (int h = 0; h < GH; ++h) {
-              ov[h] = h < p.G ? ldcg_f32(p.ws_o + part(i, h) * kD + d) : 0.f;
-              mv[h] = h < p.G ? ldcg_f32(p.ws_ml + part(i, h) * 2) : ninf;
-            }
-#pragma unroll
-            for (int h = 0; h < GH; ++h) acc[h] += (mv[h] == ninf ? 0.f : fast_exp2(mv[h] - red_ml[(h < p.G ? h : 0) * 2])) * ov[h];
-          }
-#pragma unroll
-          for (int h = 0; h < GH; ++h) {
-            if (h < p.G) {
-              const float mg = red_ml[h * 2 + 0], lg = red_ml[h * 2 + 1];
-              const int hq = hv * p.G + h;
-              typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
-              op[d] = E::from_float(acc[h] * (vscale / lg));
-              if (p.lse_out != nullptr && d == 0) p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
-            }
-          }
-        }
+    }
+    named_bar_sync(1, kConsumerWarps * 32);   // every thread's stores are issued; the release is cumulative over them
+    if (tid == 0) {
+      if constexpr (kAsyncPublish) {
+        // hand the release to the helper warp: request ring slot, then the sequence word it polls (CTA-scope release)
+        pub_ring_push(pub_req, reinterpret_cast<unsigned long long>(tk.cnt + kPlanCounterWords / 2));
+      } else {
+        merge_publish(tk.cnt + kPlanCounterWords / 2);
       }
+    }
+    return;
+  }
+  // ---- the last CTA of the pair: wait for the others' partials, then reduce ----
+  if (tid == 0) {
+    int* cnt = tk.cnt;
+    int* pub = cnt + kPlanCounterWords / 2;
+    int seen;
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(pub) : "memory");
+    } while (seen < np - 1);
+    *cnt = 0;   // re-arm both counters for the next launch
+    *pub = 0;
+  }
+  named_bar_sync(1, kConsumerWarps * 32);
+  const int own = (int)blockIdx.x - c_lo;
+  auto part = [&](int i, int h) { return ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + h; };
+  constexpr int CH = GH == 8 ? 4 : 2;   // partials per round: their loads are all in flight at once (one L2 round trip)
+  float ms[GH], ls[GH], os[GH];
+#pragma unroll
+  for (int h = 0; h < GH; ++h) { ms[h] = ninf; ls[h] = 0.f; os[h] = 0.f; }   // partials are folded in index order (deterministic)
+  float2* ml_s = reinterpret_cast<float2*>(mrg);   // [CH][GH] (m, l) of the round, loaded once and shared through smem
+  for (int i0 = 0; i0 < np; i0 += CH) {
+    float ov[CH][GH];
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+      for (int h = 0; h < GH; ++h) {
+        const int i = i0 + j;
+        ov[j][h] = (i == own) ? acc[h] : ((i < np && h < p.G) ? ldcg_f32(p.ws_o + part(i, h) * kD + tid) : 0.f);
+      }
+    if (tid < CH * GH) {
+      const int j = tid / GH, h = tid % GH, i = i0 + j;
+      float2 v = make_float2(ninf, 0.f);
+      if (i == own) {
+#pragma unroll
+        for (int hh = 0; hh < GH; ++hh)
+          if (hh == h) v = make_float2(mg[hh], lg[hh]);
+      } else if (i < np && h < p.G) {
+        v = ldcg_f32x2(p.ws_ml + part(i, h) * 2);
+      }
+      ml_s[tid] = v;
+    }
+    named_bar_sync(1, kConsumerWarps * 32);
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+      for (int h = 0; h < GH; ++h) {
+        const float2 mv = ml_s[j * GH + h];
+        const float mn = fmaxf(ms[h], mv.x);
+        const float a = (ms[h] == ninf) ? 0.f : fast_exp2(ms[h] - mn);
+        const float b = (mv.x == ninf) ? 0.f : fast_exp2(mv.x - mn);
+        os[h] = os[h] * a + ov[j][h] * b;
+        ls[h] = ls[h] * a + mv.y * b;
+        ms[h] = mn;
+      }
+    if (i0 + CH < np) named_bar_sync(1, kConsumerWarps * 32);   // the next round overwrites ml_s
+  }
+  using E = Elem<QDT>;
+#pragma unroll
+  for (int h = 0; h < GH; ++h) {
+    if (h < p.G) {
+      const int hq = hv * p.G + h;
+      typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+      op[tid] = E::from_float(os[h] * (vscale / ls[h]));
+      if (p.lse_out != nullptr && tid == 0) p.lse_out[(int64_t)s * p.Hq + hq] = (ms[h] + fast_log2(ls[h])) * 0.6931471805599453f;
+    }
   }
 }
 

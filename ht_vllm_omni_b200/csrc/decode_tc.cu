@@ -19,19 +19,25 @@
 // FP8 operands without losing the 16-bit activations: the bf16 query is split EXACTLY into two e4m3 terms
 // q*2^k = hi + lo (8 significant bits = 4 + 4) that occupy N columns h and 8+h of the same MMA, and the probabilities are
 // split the same way (p*16 = hi + lo/16), so the column pairs are recombined in fp32 after the MMA.
+#include <cstdio>
+#include <cstdlib>
+
 #include "decode_common.cuh"
 
 namespace b200attn {
 
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 224;               // 4 softmax warps + producer + MMA issuer + publish helper
 constexpr int kTcTile = 128;                 // tokens per MMA tile (= 2 plan tiles of 64)
-constexpr int kTcStages = 3;                 // depth of the K ring and of the V ring
+#ifndef B200_TC_STAGES
+#define B200_TC_STAGES 3
+#endif
+constexpr int kTcStages = B200_TC_STAGES;    // depth of the K ring and of the V ring (2: three CTAs fit per SM, see below)
 constexpr int kTcTileBytes = kTcTile * kD;   // 16 KiB (fp8)
 constexpr int kTcBoxBytes = kChunkTokens * kD;
 constexpr int kTcQRawBytes = 8 * kD * 2;     // 8 query rows of 16-bit elements
 constexpr int kTcQopBytes = 16 * kD;         // 16 rows (8 hi + 8 lo) of e4m3
 constexpr int kTcPBytes = kTcTile * 16;      // [token][8 hi + 8 lo] e4m3
-constexpr int kTcScratchFloats = 160;
+constexpr int kTcScratchFloats = 176;         // 156..173: publish request ring (9 x 8 bytes)
 constexpr int kTcTmemCols = 64;              // S0 [0,16) S1 [16,32) O [32,48)
 constexpr float kTcMargin = 4.0f;            // the reference maximum is raised when a logit exceeds it by 2^4
 constexpr float kTcPShift = 4.0f;            // p' = p * 2^4, so p' <= 2^8 < 448 (e4m3 max)
@@ -40,14 +46,19 @@ struct TcSmem {
   static constexpr int kK = 0;
   static constexpr int kV = kK + kTcStages * kTcTileBytes;
   static constexpr int kQRaw = kV + kTcStages * kTcTileBytes;
-  static constexpr int kQop = kQRaw + 2 * kTcQRawBytes;
+  static constexpr int kQop = kQRaw + kTcQRawBytes;
   static constexpr int kP = kQop + 2 * kTcQopBytes;
   static constexpr int kScratch = kP + 2 * kTcPBytes;
   static constexpr int kBars = kScratch + kTcScratchFloats * 4;
   static constexpr int kNumBars = 4 * kTcStages + 16;
   static constexpr int kTmemPtr = kBars + kNumBars * 8;
-  static constexpr int kTotal = kTmemPtr + 16 + 1024;  // + manual 1024-byte alignment
-  static_assert(kTotal <= 113 * 1024, "two CTAs per SM must fit");
+  static constexpr int kTotal = kTmemPtr + 16;
+  // The grid is 2 CTAs per SM, but a CTA is sized so that THREE fit (75 KiB, <= 112 registers): with programmatic
+  // dependent launch the first CTA of the next kernel on this stream becomes resident beside the two running ones, runs
+  // its prologue and prefetches its first K/V tiles, so launch latency, metadata fetch and the merge tail of one kernel
+  // overlap the streaming of its neighbours.
+  static constexpr int kCtasPerSm = kTcStages <= 2 ? 3 : 2;
+  static_assert(kTotal <= (kCtasPerSm == 3 ? 75 : 113) * 1024, "smem budget exceeded");
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -157,11 +168,12 @@ struct TcCursor {
 };
 
 template <int QDT>
-__global__ void __launch_bounds__(kTcThreads, 2)
+__global__ void __launch_bounds__(kTcThreads, TcSmem::kCtasPerSm)
 decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v, const DecodeParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));   // generic pointer to the aligned base
+  extern __shared__ __align__(1024) uint8_t smem_raw[];   // 128-byte-swizzled tiles need 1024-byte alignment
+  const uint32_t base = smem_u32(smem_raw);
+  if (base & 1023u) __trap();
+  uint8_t* gen = smem_raw;
   const uint32_t k_base = base + TcSmem::kK, v_base = base + TcSmem::kV;
   const uint32_t qraw_base = base + TcSmem::kQRaw, qop_base = base + TcSmem::kQop, p_base = base + TcSmem::kP;
   float* scratch = reinterpret_cast<float*>(gen + TcSmem::kScratch);
@@ -192,6 +204,14 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
     return;
   }
 
+  if (threadIdx.x == 4 * 32) {
+    // warm the metadata the producer's first tile depends on (sequence length, block ids, scales) while the CTA sets up
+    const int row = p.row_map ? __ldg(p.row_map + cs.x) : cs.x;
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p.seq_lens + cs.x));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p.block_table + (int64_t)row * p.bt_stride + (cs.z * 4) / p.cpb));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p.k_scale));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p.v_scale));
+  }
   if (threadIdx.x == 0) {
     for (int i = 0; i < kTcStages; ++i) {
       mbar_init(kfull(i), 1); mbar_init(kempty(i), 1);
@@ -203,6 +223,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       mbar_init(sfull(i), 1); mbar_init(sempty(i), 4);
       mbar_init(pfull(i), 4); mbar_init(pempty(i), 1);
     }
+    *reinterpret_cast<volatile unsigned long long*>(scratch + 156) = 0ull;
     mbar_fence_init();
     prefetch_tensormap(&tm_k);
     prefetch_tensormap(&tm_v);
@@ -231,12 +252,12 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
     int kvh = 0;
     auto issue_q = [&]() {
       const uint32_t slot = cur.sg & 1;
-      mbar_wait(qempty(slot), ((cur.sg >> 1) & 1) ^ 1);
-      if (lane == 0) mbar_arrive_expect_tx(qfull(slot), (uint32_t)p.G * kD * 2);
+      mbar_wait(qempty(0), (cur.sg & 1) ^ 1);   // one raw-query buffer: the split of segment sg-1 has consumed it
+      if (lane == 0) mbar_arrive_expect_tx(qfull(0), (uint32_t)p.G * kD * 2);
       __syncwarp();
       if (lane < p.G) {
         const uint16_t* src = qptr + (int64_t)cur.seg_s * p.q_stride_t + (int64_t)(cur.seg_hv * p.G + lane) * p.q_stride_h;
-        bulk_load_1d(qraw_base + slot * kTcQRawBytes + lane * (kD * 2), src, kD * 2, qfull(slot));
+        bulk_load_1d(qraw_base + lane * (kD * 2), src, kD * 2, qfull(0));
       }
       q_issued = true;
     };
@@ -329,6 +350,18 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       issue_pv();
       if (have && cq.first()) issue_qk();
     }
+  } else if (warp == 6) {
+    // =========================================== publish helper ===========================================
+    // Takes the release fence + counter bump of the in-kernel merge off the softmax warps: a memory round trip costs
+    // microseconds while the CTA's own KV stream saturates HBM, and the softmax warps would stall the whole pipeline on it.
+    volatile unsigned long long* ring = reinterpret_cast<volatile unsigned long long*>(scratch + 156);
+    for (uint32_t k = 0;; ++k) {
+      while (pub_ring_count(ring) <= k) __nanosleep(64);
+      const unsigned long long req = ring[1 + (k & 7)];
+      if (req == 0) break;   // the softmax warps are done
+      if (lane == 0) merge_publish(reinterpret_cast<int*>(req));
+      __syncwarp();
+    }
   } else {
     // =========================================== softmax warps ===========================================
     pdl_wait();
@@ -339,57 +372,67 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
     float* wmax = scratch + 16;                              // [4][8]  per-warp tile maxima
     volatile int* flags = reinterpret_cast<volatile int*>(scratch + 48);  // [2][4] "a logit left the window" votes
     float* red_l = scratch + 56;                             // [4][8]  per-warp row sums
-    float* red_o = scratch + 88;                             // merge scratch (32 floats)
-    float* red_ml = scratch + 120;                           // merge scratch (16 floats)
-    volatile int* hand = reinterpret_cast<volatile int*>(scratch + 136);
+    float* mrg = scratch + 88;                               // merge scratch (64 floats)
+    volatile int* hand = reinterpret_cast<volatile int*>(scratch + 152);
+    volatile unsigned long long* pub_req = reinterpret_cast<volatile unsigned long long*>(scratch + 156);   // request ring [1 + 8]
+    MergeTicket tk = {};
     const float ninf = -INFINITY;
     TcCursor cur; cur.init(cs);
     uint32_t it = 0;
     float m_ref[8], l_part[8], crow[8];
     bool stamped = false;
+    long long cyc_wait = 0, cyc_work = 0;
+
+    // ---------------- per segment: split the 16-bit query rows into e4m3 hi / lo operand rows (Qop) ----------------
+    // Runs one segment AHEAD of the tile loop (cursor `qc`): the next segment's operand is published before this segment's
+    // epilogue, so the MMA warp can issue the next QK right behind the last PV.
+    TcCursor qc; qc.init(cs);
+    auto prep_q = [&]() {
+      const uint32_t slot = qc.sg & 1;
+      const int kvh = qc.seg_hv / p.gsplit;
+      mbar_wait(qfull(0), qc.sg & 1);
+      const int h = tid >> 4, part = tid & 15;   // 16 threads per head, 8 consecutive head dims each
+      uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+      if (h < p.G) raw = lds128(qraw_base + h * (kD * 2) + part * 16);
+      float f[8];
+      f[0] = q_to_float<QDT>(raw.x & 0xffff); f[1] = q_to_float<QDT>(raw.x >> 16);
+      f[2] = q_to_float<QDT>(raw.y & 0xffff); f[3] = q_to_float<QDT>(raw.y >> 16);
+      f[4] = q_to_float<QDT>(raw.z & 0xffff); f[5] = q_to_float<QDT>(raw.z >> 16);
+      f[6] = q_to_float<QDT>(raw.w & 0xffff); f[7] = q_to_float<QDT>(raw.w >> 16);
+      float amax = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(f[i]));
+#pragma unroll
+      for (int off = 1; off < 16; off <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+      // exact power-of-two pre-scale that puts the row maximum in [128, 256); undone on the logits
+      const uint32_t eb = (__float_as_uint(amax) >> 23) & 0xffu;
+      const bool norm = eb >= 16 && eb < 255;
+      const float inv = norm ? __uint_as_float((261u - eb) << 23) : 1.0f;
+      const float fct = norm ? __uint_as_float((eb - 7u) << 23) : 1.0f;
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) split_pair(f[2 * i] * inv, f[2 * i + 1] * inv, 16.0f, hi[i], lo[i]);
+      mbar_wait(qopempty(slot), ((qc.sg >> 1) & 1) ^ 1);   // the MMAs of segment sg-2 are done with this slot
+      // K-major, no swizzle: 8x16-byte core matrices; byte (row r, d) at (r/8)*1024 + (d/16)*128 + (r%8)*16 + d%16
+      const uint32_t qa = qop_base + slot * kTcQopBytes + (part >> 1) * 128 + h * 16 + (part & 1) * 8;
+      asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(hi[0] | (hi[1] << 16)), "r"(hi[2] | (hi[3] << 16)) : "memory");
+      asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa + 1024), "r"(lo[0] | (lo[1] << 16)), "r"(lo[2] | (lo[3] << 16)) : "memory");
+      if (part == 0) {
+        const float kscale = __ldg(p.k_scale + (int64_t)kvh * p.scale_stride);
+        cs_sm[slot * 8 + h] = (h < p.G) ? fct * p.sm_scale_log2 * kscale : 0.f;
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+      if (lane == 0) {
+        mbar_arrive(qopfull(slot));
+        mbar_arrive(qempty(0));
+      }
+    };
+    if (qc.next_segment(p)) prep_q();
 
     while (cur.next_tile(p)) {
       if (cur.first()) {
-        // ---------------- new segment: split the 16-bit query rows into e4m3 hi / lo operand rows ----------------
         const uint32_t slot = cur.sg & 1;
-        const int kvh = cur.seg_hv / p.gsplit;
-        mbar_wait(qfull(slot), (cur.sg >> 1) & 1);
-        const int h = tid >> 4, part = tid & 15;   // 16 threads per head, 8 consecutive head dims each
-        uint4 raw = make_uint4(0u, 0u, 0u, 0u);
-        if (h < p.G) raw = lds128(qraw_base + slot * kTcQRawBytes + h * (kD * 2) + part * 16);
-        float f[8];
-        f[0] = q_to_float<QDT>(raw.x & 0xffff); f[1] = q_to_float<QDT>(raw.x >> 16);
-        f[2] = q_to_float<QDT>(raw.y & 0xffff); f[3] = q_to_float<QDT>(raw.y >> 16);
-        f[4] = q_to_float<QDT>(raw.z & 0xffff); f[5] = q_to_float<QDT>(raw.z >> 16);
-        f[6] = q_to_float<QDT>(raw.w & 0xffff); f[7] = q_to_float<QDT>(raw.w >> 16);
-        float amax = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(f[i]));
-#pragma unroll
-        for (int off = 1; off < 16; off <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
-        // exact power-of-two pre-scale that puts the row maximum in [128, 256); undone on the logits
-        const uint32_t eb = (__float_as_uint(amax) >> 23) & 0xffu;
-        const bool norm = eb >= 16 && eb < 255;
-        const float inv = norm ? __uint_as_float((261u - eb) << 23) : 1.0f;
-        const float fct = norm ? __uint_as_float((eb - 7u) << 23) : 1.0f;
-        uint32_t hi[4], lo[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) split_pair(f[2 * i] * inv, f[2 * i + 1] * inv, 16.0f, hi[i], lo[i]);
-        mbar_wait(qopempty(slot), ((cur.sg >> 1) & 1) ^ 1);   // the MMAs of segment sg-2 are done with this slot
-        // K-major, no swizzle: 8x16-byte core matrices; byte (row r, d) at (r/8)*1024 + (d/16)*128 + (r%8)*16 + d%16
-        const uint32_t qa = qop_base + slot * kTcQopBytes + (part >> 1) * 128 + h * 16 + (part & 1) * 8;
-        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(hi[0] | (hi[1] << 16)), "r"(hi[2] | (hi[3] << 16)) : "memory");
-        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa + 1024), "r"(lo[0] | (lo[1] << 16)), "r"(lo[2] | (lo[3] << 16)) : "memory");
-        if (part == 0) {
-          const float kscale = __ldg(p.k_scale + (int64_t)kvh * p.scale_stride);
-          cs_sm[slot * 8 + h] = (h < p.G) ? fct * p.sm_scale_log2 * kscale : 0.f;
-        }
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (lane == 0) {
-          mbar_arrive(qopfull(slot));
-          mbar_arrive(qempty(slot));
-        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           crow[i] = cs_sm[slot * 8 + i];
@@ -397,10 +440,19 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
           l_part[i] = 0.f;
         }
       }
+      // The merge ticket of a cut segment is drawn a few tiles BEFORE its end, so the round trip of the atomic hides behind
+      // the remaining tiles (any order of arrival is valid: the last to draw merges, and it waits for the others' partials).
+      if (tid == 0 && p.fused_merge && cur.u == max(cur.m - 4, 0)) {
+        const bool whole_seg = (cur.seg_tile0 == 0) && ((cur.seg_tile0 + cur.seg_n) * kTileTokens >= cur.seg_L);
+        if (!whole_seg) tk = merge_draw_ticket(p, cur.seg_hv, cur.seg_L, __ldg(p.plan + kPlanPrefixOffset + cur.seg_s));
+      }
 
       // ---------------- one 128-token tile: S^T row of this thread's token ----------------
       const uint32_t b = it & 1;
+      const long long c0 = clock64();
       mbar_wait(sfull(b), (it >> 1) & 1);
+      const long long c1 = clock64();
+      cyc_wait += c1 - c0;
       tc_fence_after();
       if (!stamped && tid == 0) { dbg_stamp(p, 3); stamped = true; }
       uint32_t r[16];
@@ -483,7 +535,9 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       __syncwarp();
       if (lane == 0) mbar_arrive(pfull(b));
       ++it;
+      cyc_work += clock64() - c1;
 
+      if (cur.last() && qc.next_segment(p)) prep_q();   // publish the next segment's operand before this epilogue
       if (cur.last()) {
         // ---------------- segment end: O^T row of this thread's head dim, row sums, output or partial ----------------
         if (tid == 0 && cur.remaining <= 0) dbg_stamp(p, 4);
@@ -507,18 +561,20 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
         const int pslot = cur.sg == 0 ? 0 : 1;
         const int d = tid;
         using E = Elem<QDT>;
+        float accv[8], mgv[8], lgv[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
+          const float lg = (red_l[i] + red_l[8 + i]) + (red_l[16 + i] + red_l[24 + i]);
+          const float acc = __uint_as_float(o[i]) + __uint_as_float(o[8 + i]) * 0.0625f;
+          const float mg = m_ref[i] - kTcPShift;   // p' = 2^(x - mg)
+          accv[i] = acc; mgv[i] = mg; lgv[i] = lg;
           if (i < p.G) {
-            const float lg = (red_l[i] + red_l[8 + i]) + (red_l[16 + i] + red_l[24 + i]);
-            const float acc = __uint_as_float(o[i]) + __uint_as_float(o[8 + i]) * 0.0625f;
-            const float mg = m_ref[i] - kTcPShift;   // p' = 2^(x - mg)
             if (whole) {
               const int hq = hv * p.G + i;
               typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
               op[d] = E::from_float(acc * (vscale / lg));
               if (p.lse_out != nullptr && d == 0) p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
-            } else {
+            } else if (!p.fused_merge) {
               const size_t pidx = ((size_t)blockIdx.x * 2 + pslot) * kMaxGroup + i;
               __stcg(p.ws_o + pidx * kD + d, acc);
               if (d == 0) __stcg(reinterpret_cast<float2*>(p.ws_ml + pidx * 2), make_float2(mg, lg));
@@ -526,13 +582,19 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
           }
         }
         if (!whole && p.fused_merge) {
-          const int pfx = __ldg(p.plan + kPlanPrefixOffset + s);
-          fused_merge_tail<QDT, 8>(p, s, hv, L, pfx, vscale, tid, red_o, red_ml, hand);
+          unsigned long long tm0 = 0, tm1 = 0;
+          if (p.dbg != nullptr && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm0));
+          fused_merge_tail<QDT, 8, true>(p, s, hv, vscale, tid, pslot, tk, accv, mgv, lgv, mrg, hand, pub_req);
+          if (p.dbg != nullptr && tid == 0) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm1));
+            p.dbg[(size_t)blockIdx.x * 8 + (hand[0] > 0 ? 7 : 6)] += tm1 - tm0;   // 6: publish calls, 7: merge calls
+          }
         }
         named_bar_sync(1, 128);
       }
     }
     if (tid == 0) dbg_stamp(p, 5);
+    if (tid == 0) pub_ring_push(pub_req, 0ull);   // tell the publish helper to leave
   }
 
   // teardown: every role is done with TMEM (the softmax warps waited for the last PV)
@@ -555,6 +617,12 @@ static int launch_tc(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeP
   if (!configured) {
     if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem::kTotal), "cudaFuncSetAttribute(decode_tc smem)"))
       return B200ATTN_ECUDA;
+    (void)cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (getenv("B200ATTN_VERBOSE")) {
+      int nb = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, kTcThreads, TcSmem::kTotal);
+      fprintf(stderr, "[b200attn] decode_tc: %d B smem / CTA, %d stages, occupancy %d CTAs / SM\n", TcSmem::kTotal, kTcStages, nb);
+    }
     configured = true;
   }
   void* args[] = {(void*)&tk, (void*)&tv, (void*)&p};

@@ -1,0 +1,47 @@
+"""Debug: %globaltimer timelines of CONSECUTIVE decode launches on one stream (PDL on), to see how the prologue / tail of
+neighbouring kernels overlap.  Env: B200_TC, B200_FUSED (1), B200_FRESH (-1), B200_WRITE (0: decode only, 1: kv_write between)."""
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
+import ctypes, numpy as np, torch
+import ht_vllm_omni_b200.ops as ops
+lib = ops.load_library()
+dev = torch.device("cuda")
+B, L, Hq, Hkv, D, bs = 64, 4096, 16, 2, 128, 16
+nblk = L // bs; nb = B * nblk + 8
+layers = 8
+fused = int(os.environ.get("B200_FUSED", "1")); fresh = int(os.environ.get("B200_FRESH", "-1")); wr = int(os.environ.get("B200_WRITE", "0"))
+bt = torch.randperm(nb, generator=torch.Generator().manual_seed(1))[: B * nblk].to(torch.int32).reshape(B, nblk).to(dev)
+lens = torch.full((B,), L, dtype=torch.int32, device=dev)
+caches = [torch.randint(0, 0x78, (nb, 2, Hkv, bs, D), dtype=torch.uint8, device=dev).permute(0, 1, 3, 2, 4).unbind(1) for _ in range(layers)]
+q = torch.randn(B, Hq, D, device=dev).to(torch.bfloat16); out = torch.zeros_like(q)
+kn = torch.randn(B, Hkv, D, device=dev).to(torch.bfloat16); vn = torch.randn(B, Hkv, D, device=dev).to(torch.bfloat16)
+slots = (bt.to(torch.int64)[:, (L - 1) // bs] * bs + (L - 1) % bs).contiguous()
+ks = torch.full((Hkv,), 0.01, device=dev); vs = torch.full((Hkv,), 0.01, device=dev)
+ws = ops.DecodeWorkspace(dev, B, torch.uint8, num_ctas=int(os.environ.get("B200_CTAS", "0")) or None); ws.make_plan(lens, Hq, Hkv)
+nc = ws.num_ctas
+buf = torch.zeros(layers, nc * 8, dtype=torch.int64, device=dev)
+lib.b200attn_set_option(b"pdl", int(os.environ.get("B200_PDL", "1")))
+lib.b200attn_set_option(b"tc", int(os.environ.get("B200_TC", "1")))
+fn = lib.b200attn_debug_set_timeline_buffer; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
+for rep in range(2):
+    buf.zero_()
+    for l in range(layers):
+        fn(buf[l].data_ptr())
+        if wr:
+            torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs)
+        ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, nc, None, None, fresh, bool(fused))
+    torch.cuda.synchronize()
+fn(None)
+t = buf.cpu().numpy().reshape(layers, nc, 8).astype(np.float64)
+t0 = t[0][t[0][:, 1] > 0][:, 0].min()
+print(f"tc={os.environ.get('B200_TC','1')} fused={fused} fresh={fresh} write={wr} ctas={nc}: per launch, us relative to launch 0's first CTA entry")
+prev_exit = None
+for l in range(layers):
+    a = t[l][t[l][:, 1] > 0]
+    e = (a[:, 0] - t0) / 1e3; d = (a[:, 3] - t0) / 1e3; lt = (a[:, 4] - t0) / 1e3; x = (a[:, 5] - t0) / 1e3
+    w6 = a[:, 6] / 1e3; w7 = a[:, 7] / 1e3
+    slow = np.argsort(lt)[-3:]
+    print(f"            publish calls per CTA: p50 {np.median(w6):5.2f} p90 {np.percentile(w6,90):5.2f} max {w6.max():5.2f} us | merge calls: p50 {np.median(w7[w7>0]):5.2f} p90 {np.percentile(w7[w7>0],90):5.2f} max {w7.max():5.2f} us | slowest: " + ", ".join(f"lt {lt[i]:.1f} pub {w6[i]:.2f} mrg {w7[i]:.2f}" for i in slow))
+    gap = "" if prev_exit is None else f" | period {x.max() - prev_exit:6.2f}"
+    print(f"  launch {l}: entry min {e.min():7.2f} p50 {np.median(e):7.2f} max {e.max():7.2f} | first data p50 {np.median(d):7.2f} | last tile p50 {np.median(lt):7.2f} max {lt.max():7.2f} | exit min {x.min():7.2f} max {x.max():7.2f}{gap}")
+    prev_exit = x.max()
