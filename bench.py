@@ -285,7 +285,8 @@ def run_ours(args, w):
         for l in range(NL):
             kc, vc = caches[l]
             torch.ops.b200attn.kv_write(kn[l], vn[l], kc, vc, step_slots, k_scale, v_scale)
-            ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale)
+            # fresh_tokens=1: a decode step's KV write touched only the newest position of each row (what backend.py passes)
+            ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale, fresh_tokens=1)
         if gathered is not None:
             dist.all_gather_into_tensor(gathered, out)
 
@@ -367,24 +368,42 @@ def run_ours(args, w):
         ms_e2e = float(t.item())
     ms_e2e_per_step = ms_e2e / args.steps
 
-    # ---- (3) roofline leg: the split-KV decode kernel alone, one event pair per launch, PDL off so it runs isolated ----
+    # ---- (3) roofline leg: the decode kernel alone (split-KV + in-kernel merge, exactly the launch the step makes), NL launches
+    # over the NL distinct layer caches captured as one CUDA graph with PDL off (no overlap between neighbours), CUDA events
+    # around the replays on the launching stream; duration per launch = elapsed / launches ----
     lib.b200attn_set_option(b"pdl", 0)
     ws.make_plan(d_lens, Hq, Hkv)
     torch.cuda.synchronize()
-    evs = []
-    reps = max(1, min(args.steps, 10))
-    for r in range(reps + 1):
+
+    def decode_only():
         for l in range(NL):
             kc, vc = caches[l]
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            ops.launch_split_decode(q[l], kc, vc, d_bt, d_lens, out[l], ws.plan, ws.workspace, k_scale, v_scale, sm_scale, ws.num_ctas)
-            b.record()
-            if r > 0:   # first sweep = warm-up
-                evs.append((a, b))
+            ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale)
+
+    reps = max(1, min(args.steps, 10))
+    kgraph = torch.cuda.CUDAGraph()
+    try:
+        with torch.cuda.stream(side):
+            decode_only()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(kgraph):
+            decode_only()
+        run_k = kgraph.replay
+    except Exception:  # noqa: BLE001
+        torch.cuda.synchronize()
+        run_k = decode_only
+    for _ in range(2):
+        run_k()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        run_k()
+    b.record()
     torch.cuda.synchronize()
     lib.b200attn_set_option(b"pdl", 1)
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    evs = [None] * (reps * NL)
+    kern_ms = a.elapsed_time(b) / (reps * NL)
     sampler.stop()
 
     dec_b, wr_b = algorithmic_bytes(lens_np, Hq, Hkv, D, bs, s_kv)
@@ -409,7 +428,8 @@ def run_ours(args, w):
     line = {
         "metric": "paged_decode_attn_hbm_gbs", "value": gbs, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "fp8_e4m3 KV / bf16 Q,O / f16 HMMA, fp32 accumulate" if fp8 else "bf16 KV,Q,O / bf16 HMMA, fp32 accumulate",
+        "dtype": "fp8_e4m3 KV / bf16 Q,O / tcgen05 kind::f8f6f4 (exact hi+lo e4m3 split of Q and P), fp32 accumulate" if (fp8 and Hq // Hkv <= 8) else
+                 "fp8_e4m3 KV / bf16 Q,O / f16 HMMA, fp32 accumulate" if fp8 else "bf16 KV,Q,O / bf16 HMMA, fp32 accumulate",
         "data": "synthetic (N(0,1) tokens written through the KV-write path; random block permutation)",
         "config": workload_config(args, w, ws.num_ctas),
         "tok_s": B / (ms_per_step * 1e-3),
@@ -419,7 +439,7 @@ def run_ours(args, w):
                 "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3)},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "achieved": kern_gbs, "peak": peak, "unit": "GB/s", "frac": kern_gbs / peak,
-                     "traffic": None, "kernel": "b200attn::decode_kernel (split-KV paged flash-decoding)",
+                     "traffic": None, "kernel": ("b200attn::decode_tc_kernel" if (fp8 and Hq // Hkv <= 8) else "b200attn::decode_kernel") + " (split-KV paged flash-decoding, in-kernel merge; CUDA graph of one launch per layer cache, PDL off)",
                      "algorithmic_bytes_per_launch": dec_b, "avg_launch_us": kern_ms * 1e3, "launches_timed": len(evs),
                      "peak_source": peak_src},
         "cpu_baseline": cpu,
