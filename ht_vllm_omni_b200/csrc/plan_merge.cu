@@ -102,16 +102,20 @@ struct MergeParams {
   int Hq, G, gsplit, D;
 };
 
+// One CTA per (pair, head): the partials of a pair can be many (a long sequence in a small batch is cut across the whole
+// grid), so pass 1 spreads them over all 128 threads and pass 2 over the 4 warps, each lane owning 4 head dims (float4,
+// 8 independent loads in flight per thread).
 template <int ODT>
 __global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
-  extern __shared__ float wts[];  // [G][n_parts] normalised weights
-  __shared__ float lse_s[kMaxGroup];
+  extern __shared__ float wts[];  // [n_parts] normalised weights of this head
+  __shared__ float red[4];
+  __shared__ float4 osum[4][32];
   pdl_wait();
   pdl_launch_dependents();
   const int32_t* plan = p.plan;
   const int total = plan[0], tpc = plan[1], Hv = plan[4];
   if (total <= 0) return;
-  const int pair = blockIdx.x;
+  const int pair = blockIdx.x, head = blockIdx.y;
   const int s = pair / Hv, hv = pair - s * Hv;
   const int32_t* prefix = plan + kPlanPrefixOffset;
   const int nt = prefix[s + 1] - prefix[s];
@@ -123,49 +127,51 @@ __global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
   const int np = c_hi - c_lo + 1;
   const int slot_lo = (x0 == (long long)c_lo * tpc) ? 0 : 1;  // later CTAs start on this pair: slot 0
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  auto pidx_of = [&](int i) { return ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head; };
 
-  // pass 1: per head, global max / sum over the partials with warp shuffles; weights to smem
-  for (int head = wid; head < p.G; head += 4) {
-    float mg = -INFINITY;
-    for (int i = lane; i < np; i += 32) {
-      const size_t pidx = ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head;
-      mg = fmaxf(mg, p.ws_ml[pidx * 2]);
-    }
+  // pass 1: global max / sum over the partials (block reduction), normalised weights to smem
+  float mg = -INFINITY;
+  for (int i = tid; i < np; i += 128) mg = fmaxf(mg, p.ws_ml[pidx_of(i) * 2]);
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
-    float lg = 0.f;
-    for (int i = lane; i < np; i += 32) {
-      const size_t pidx = ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head;
-      const float wgt = fast_exp2(p.ws_ml[pidx * 2] - mg);
-      wts[head * np + i] = wgt;
-      lg += p.ws_ml[pidx * 2 + 1] * wgt;
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
-    const float inv = 1.0f / lg;
-    for (int i = lane; i < np; i += 32) wts[head * np + i] *= inv;
-    if (lane == 0) lse_s[head] = (mg + fast_log2(lg)) * 0.6931471805599453f;
-  }
+  for (int off = 16; off > 0; off >>= 1) mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, off));
+  if (lane == 0) red[wid] = mg;
   __syncthreads();
-
-  // pass 2: weighted sum of the partial outputs; consecutive threads -> consecutive head dims
+  mg = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+  __syncthreads();
+  float lg = 0.f;
+  for (int i = tid; i < np; i += 128) {
+    const float2 ml = *reinterpret_cast<const float2*>(p.ws_ml + pidx_of(i) * 2);
+    const float wgt = fast_exp2(ml.x - mg);
+    wts[i] = wgt;
+    lg += ml.y * wgt;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, off);
+  if (lane == 0) red[wid] = lg;
+  __syncthreads();
+  lg = (red[0] + red[1]) + (red[2] + red[3]);
   const int kvh = hv / p.gsplit;
   const float vscale = p.v_scale ? p.v_scale[(int64_t)kvh * p.scale_stride] : 1.0f;
-  using E = Elem<ODT>;
-  for (int idx = tid; idx < p.G * p.D; idx += 128) {
-    const int head = idx / p.D, d = idx - head * p.D;
-    float acc = 0.f;
-    const float* wh = wts + head * np;
-#pragma unroll 4
-    for (int i = 0; i < np; ++i) {
-      const size_t pidx = ((size_t)(c_lo + i) * 2 + (i == 0 ? slot_lo : 0)) * kMaxGroup + head;
-      acc += wh[i] * __ldg(p.ws_o + pidx * p.D + d);
-    }
-    const int hq = hv * p.G + head;
-    typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
-    op[d] = E::from_float(acc * vscale);
-    if (d == 0 && p.lse_out) p.lse_out[(int64_t)s * p.Hq + hq] = lse_s[head];
+  const float onorm = vscale / lg;
+
+  // pass 2: weighted sum; warp w folds partials w, w+4, ... in index order, lane = 4 consecutive head dims
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+  for (int i = wid; i < np; i += 4) {
+    const float w = wts[i];
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(p.ws_o + pidx_of(i) * p.D) + lane);
+    acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z; acc.w += w * v.w;
   }
+  osum[wid][lane] = acc;
+  __syncthreads();
+  const float* os = reinterpret_cast<const float*>(&osum[0][0]);
+  const int d = tid;
+  const float o = (os[d] + os[128 + d]) + (os[256 + d] + os[384 + d]);
+  using E = Elem<ODT>;
+  const int hq = hv * p.G + head;
+  typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h;
+  op[d] = E::from_float(o * onorm);
+  if (d == 0 && p.lse_out) p.lse_out[(int64_t)s * p.Hq + hq] = (mg + fast_log2(lg)) * 0.6931471805599453f;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -277,6 +283,10 @@ extern "C" int b200attn_merge(const void* plan, int32_t num_ctas, const void* wo
     set_error("merge: out dtype must be bf16 or fp16");
     return B200ATTN_EINVAL;
   }
+  if (head_dim != 128) {
+    set_error("merge: head_dim %d unsupported (only 128)", head_dim);
+    return B200ATTN_EINVAL;
+  }
   MergeParams p;
   p.plan = reinterpret_cast<const int32_t*>(plan);
   p.ws_o = reinterpret_cast<const float*>(workspace);
@@ -285,14 +295,14 @@ extern "C" int b200attn_merge(const void* plan, int32_t num_ctas, const void* wo
   p.v_scale = v_scale; p.scale_stride = scale_stride; p.lse_out = lse_out;
   p.Hq = num_q_heads; p.G = G; p.gsplit = gsplit; p.D = head_dim;
   const int Hv = num_kv_heads * gsplit;
-  const size_t smem = (size_t)G * num_ctas * sizeof(float);  // a pair spans at most num_ctas partials
+  const size_t smem = (size_t)num_ctas * sizeof(float);  // a pair spans at most num_ctas partials
   const void* fn = out_dtype == B200ATTN_BF16 ? (const void*)merge_kernel<B200ATTN_BF16> : (const void*)merge_kernel<B200ATTN_FP16>;
   if (smem > 48 * 1024) {
     if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute(merge smem)"))
       return B200ATTN_ECUDA;
   }
   void* args[] = {&p};
-  return launch_with_pdl(fn, dim3((unsigned)(num_seqs * Hv)), dim3(128), smem, static_cast<cudaStream_t>(stream), args);
+  return launch_with_pdl(fn, dim3((unsigned)(num_seqs * Hv), (unsigned)G), dim3(128), smem, static_cast<cudaStream_t>(stream), args);
 }
 
 extern "C" int b200attn_merge_lse(const void* parts_o, const float* parts_lse, int32_t num_parts, int64_t part_stride_o,

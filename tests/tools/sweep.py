@@ -1,5 +1,5 @@
 """BASELINE configs[2] on one B200: the synthetic paged-decode sweep (batch x context, block 16, GQA 8:1, D 128, bf16 vs FP8
-KV).  Each point times the fused-merge decode kernel as a CUDA graph of `layers` launches over distinct caches (working set
+KV).  Each point times the decode op (split-KV kernel + merge, as ops.paged_decode launches them) as a CUDA graph of `layers` launches over distinct caches (working set
 >= 2x L2 so nothing is reused), CUDA events around replays, and reports algorithmic GB/s (bench.algorithmic_bytes).
 
     python tests/tools/sweep.py [--points "1x1024,64x4096,..."] [--kv fp8,bf16] [--Hq 16 --Hkv 2] [--ctas 0] [--tc 1]
@@ -65,8 +65,7 @@ def main():
 
             def body():
                 for l in range(layers):
-                    ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs,
-                                            D ** -0.5, ws.num_ctas, None, None, -1, True)
+                    ws.decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ks, vs, D ** -0.5)   # public op (merge policy included)
             side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 body()
