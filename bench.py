@@ -462,7 +462,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--ctas", type=int, default=0, help="decode grid override (0 = 2 CTAs/SM fp8, 1 CTA/SM 16-bit)")
+    ap.add_argument("--ctas", type=int, default=0, help="decode grid override (0 = 2 CTAs/SM)")
     ap.add_argument("--allgather", default="none", choices=["none", "step"], help="NCCL all-gather of head-sharded outputs")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -181,7 +181,8 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
         self.kv_torch_dtype = torch.uint8 if kv_dtype in (torch.uint8, torch.float8_e4m3fn) else kv_dtype
         # rows = tokens: size every buffer for the largest batch vLLM can schedule
         self.max_rows = int(vllm_config.scheduler_config.max_num_batched_tokens)
-        self.workspace = ops.DecodeWorkspace(device, self.max_rows, self.kv_torch_dtype, head_dim=self.head_dim)
+        self.workspace = ops.DecodeWorkspace(device, self.max_rows, self.kv_torch_dtype, head_dim=self.head_dim,
+                                             group_size=max(1, self.num_heads_q // max(1, self.num_heads_kv)))
         self._row_lens = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
         self._row_map = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
 

@@ -27,6 +27,9 @@ namespace b200attn {
 #ifndef B200_FP8_CTAS_NT1
 #define B200_FP8_CTAS_NT1 2
 #endif
+#ifndef B200_KV16_CTAS_NT1
+#define B200_KV16_CTAS_NT1 2
+#endif
 constexpr int kQSlotBytes = kMaxGroup * kD * 2;  // 4 KiB: 16 query rows
 constexpr int kRedStride = kD + 4;               // floats; +4 keeps rows 16-byte aligned and staggers banks
 
@@ -46,13 +49,15 @@ struct Smem {
   static constexpr int kDescBytes = 3 * 32;   // 2 segment descriptors + merge hand-off words
   static constexpr int kBarBytes = 256;
   static constexpr int kFixedBytes = 2 * kQSlotBytes + kRedOBytes + kRedMlBytes + kDescBytes + kBarBytes;
-  // fp8: 3 CTAs / SM (75 KiB each) for G <= 8, 2 CTAs / SM (113 KiB) for G <= 16; 16-bit: 1 CTA / SM (227 KiB)
-  static constexpr int kCtas = KvCfg<KVT>::kFp8 ? (NT == 1 ? B200_FP8_CTAS_NT1 : 2) : 1;
+  // fp8: 2 CTAs / SM (113 KiB, 6 x 16 KiB stages).  16-bit KV, G <= 8: also 2 CTAs / SM with 2 x 32 KiB stages each -- one CTA
+  // per SM (6 stages) left the 4 consumer warps latency-bound at 75 % of HBM, two reach the copy peak (profiles/r01_sweep_*).
+  // 16-bit KV with G > 8 (234 registers) stays at 1 CTA / SM.
+  static constexpr int kCtas = KvCfg<KVT>::kFp8 ? (NT == 1 ? B200_FP8_CTAS_NT1 : 2) : (NT == 1 ? B200_KV16_CTAS_NT1 : 1);
   static constexpr int kBudget = kCtas == 3 ? 75 * 1024 : (kCtas == 2 ? 113 * 1024 : 227 * 1024);
   static constexpr int kStagesRaw = (kBudget - kFixedBytes - 1024) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTotalBytes = kStages * kStageBytes + kFixedBytes + 1024;  // +1024: manual alignment
-  static_assert(kStages >= 3, "pipeline too shallow");
+  static_assert(kStages >= 2, "pipeline too shallow");
   static_assert(kTotalBytes <= kBudget, "smem budget exceeded");
 };
 

@@ -59,7 +59,7 @@ def _cache_strides(k_cache: torch.Tensor, v_cache: torch.Tensor):
 
 
 def default_ctas(kv_dtype: torch.dtype) -> int:
-    """Persistent decode grid for this device: 2 CTAs/SM (fp8 KV) or 1 CTA/SM (16-bit KV)."""
+    """Persistent decode grid for this device: 2 CTAs/SM."""
     n = load_library().b200attn_default_ctas(DT_FP8_E4M3 if kv_dtype in _FP8_DTYPES else DT_BF16)
     if n <= 0:
         raise B200AttnError("no CUDA device: libb200attn has no CPU fallback")
@@ -218,10 +218,15 @@ def _(parts_o, parts_lse, out, lse_out) -> None:
 class DecodeWorkspace:
     """Pre-allocated, capture-safe buffers for one device: plan (int32) + split-KV partials (fp32)."""
 
-    def __init__(self, device, max_num_seqs: int, kv_dtype: torch.dtype, head_dim: int = 128, num_ctas: int | None = None):
+    def __init__(self, device, max_num_seqs: int, kv_dtype: torch.dtype, head_dim: int = 128, num_ctas: int | None = None,
+                 group_size: int = 8):
+        """`group_size` = query heads per kv head: 16-bit KV with more than 8 (the two-accumulator-set variant of the
+        kernel, one resident CTA per SM) gets half the default grid so the persistent CTAs still run as one wave."""
         self.device = torch.device(device)
         with torch.cuda.device(self.device):
             self.num_ctas = int(num_ctas) if num_ctas else default_ctas(kv_dtype)
+        if not num_ctas and kv_dtype not in _FP8_DTYPES and group_size > 8:
+            self.num_ctas = max(1, self.num_ctas // 2)
         self.max_num_seqs = max_num_seqs
         self.plan = torch.zeros(plan_numel(max_num_seqs), dtype=torch.int32, device=self.device)
         self.workspace = torch.empty(workspace_numel(head_dim, self.num_ctas), dtype=torch.float32, device=self.device)

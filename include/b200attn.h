@@ -92,7 +92,7 @@ B200ATTN_API int b200attn_kv_write(const void* key, const void* value,
  * Cuts the flat list of (sequence, kv head, 64-token tile) work items into equal contiguous
  * ranges, one per persistent CTA, entirely on the device (no host sync, capture-safe).
  * `plan` must hold b200attn_plan_bytes(num_seqs) bytes.  `num_ctas` is the decode grid: use
- * b200attn_default_ctas(kv_dtype) (2 CTAs/SM for fp8, 1 for 16-bit KV); tests pass small values
+ * b200attn_default_ctas(kv_dtype) (2 CTAs/SM); tests pass small values
  * to force many split points.  The SAME num_ctas must be given to decode and merge.
  */
 B200ATTN_API size_t b200attn_plan_bytes(int32_t max_num_seqs);

@@ -60,7 +60,7 @@ def main():
             q = torch.randn(B, Hq, D, device=dev).to(torch.bfloat16)
             out = torch.zeros(B, Hq, D, dtype=torch.bfloat16, device=dev)
             ks = torch.full((Hkv,), 0.01, device=dev); vs = torch.full((Hkv,), 0.01, device=dev)
-            ws = ops.DecodeWorkspace(dev, B, kv_t, num_ctas=a.ctas or None)
+            ws = ops.DecodeWorkspace(dev, B, kv_t, num_ctas=a.ctas or None, group_size=Hq // Hkv)
             ws.make_plan(d_lens, Hq, Hkv)
 
             def body():

@@ -23,14 +23,27 @@ buf = torch.zeros(layers, nc * 8, dtype=torch.int64, device=dev)
 lib.b200attn_set_option(b"pdl", int(os.environ.get("B200_PDL", "1")))
 lib.b200attn_set_option(b"tc", int(os.environ.get("B200_TC", "1")))
 fn = lib.b200attn_debug_set_timeline_buffer; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
-for rep in range(2):
-    buf.zero_()
+def chain():
     for l in range(layers):
         fn(buf[l].data_ptr())
         if wr:
             torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs)
         ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, nc, None, None, fresh, bool(fused))
-    torch.cuda.synchronize()
+if int(os.environ.get("B200_GRAPH", "1")):
+    # the launches are captured (debug buffer pointers are baked into the kernel parameters) and replayed, so the gaps are
+    # those of a CUDA graph, not of eager host launches
+    side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        chain()
+    torch.cuda.current_stream().wait_stream(side); torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        chain()
+    for rep in range(3):
+        buf.zero_(); g.replay(); torch.cuda.synchronize()
+else:
+    for rep in range(2):
+        buf.zero_(); chain(); torch.cuda.synchronize()
 fn(None)
 t = buf.cpu().numpy().reshape(layers, nc, 8).astype(np.float64)
 t0 = t[0][t[0][:, 1] > 0][:, 0].min()
