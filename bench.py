@@ -212,7 +212,7 @@ def run_reference(args, w):
         "note": "reference CPU backend (vLLM cpu_attn) is not compiled into the CUDA wheel in this image; this arm times the "
                 "oracle's C/OpenMP port of the reference algorithm on all host cores; ms_per_step is extrapolated to all layers",
     }
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 def workload_config(args, w, num_ctas):
@@ -346,11 +346,64 @@ def run_ours(args, w):
     h2d_bytes = sum(t.numel() * t.element_size() for t in (h_q, h_kn, h_vn, h_slots, h_lens, h_bt))
     d2h_bytes = h_out.numel() * h_out.element_size()
 
+    # The host-buffer call is pipelined in layer groups: group g's inputs travel H2D on a copy stream while group g-1
+    # computes, and its outputs travel D2H on a second copy stream while group g+1 computes (PCIe is full duplex).  The
+    # whole step -- copies, plan, 2 x NL kernels -- is one CUDA graph with three stream branches.
+    NG = int(os.environ.get("B200_E2E_GROUPS", "5"))
+    NG = NG if (NG > 0 and NL % NG == 0) else 1
+    GL = NL // NG
+    s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+    def e2e_body():
+        main = torch.cuda.current_stream()
+        s_in.wait_stream(main)
+        s_out.wait_stream(main)
+        ev_in = []
+        with torch.cuda.stream(s_in):
+            step_slots.copy_(h_slots, non_blocking=True); d_lens.copy_(h_lens, non_blocking=True); d_bt.copy_(h_bt, non_blocking=True)
+            for gi in range(NG):
+                sl = slice(gi * GL, (gi + 1) * GL)
+                q[sl].copy_(h_q[sl], non_blocking=True); kn[sl].copy_(h_kn[sl], non_blocking=True); vn[sl].copy_(h_vn[sl], non_blocking=True)
+                ev = torch.cuda.Event(); ev.record(s_in); ev_in.append(ev)
+        for gi in range(NG):
+            main.wait_event(ev_in[gi])
+            if gi == 0:
+                ws.make_plan(d_lens, Hq, Hkv)
+            for l in range(gi * GL, (gi + 1) * GL):
+                kc, vc = caches[l]
+                torch.ops.b200attn.kv_write(kn[l], vn[l], kc, vc, step_slots, k_scale, v_scale)
+                ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale, fresh_tokens=1)
+            ev = torch.cuda.Event(); ev.record(main)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev)
+                sl = slice(gi * GL, (gi + 1) * GL)
+                h_out[sl].copy_(out[sl], non_blocking=True)
+        main.wait_stream(s_in)
+        main.wait_stream(s_out)
+
+    e2e_graph = None
+    if use_graph and gathered is None:
+        try:
+            with torch.cuda.stream(side):
+                e2e_body()
+            torch.cuda.synchronize()
+            e2e_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(e2e_graph):
+                e2e_body()
+        except Exception as e:  # noqa: BLE001
+            if rank == 0:
+                print(f"# e2e graph capture failed ({type(e).__name__}: {e}); using the serial copy/step/copy path", file=sys.stderr)
+            e2e_graph = None
+            torch.cuda.synchronize()
+
     def e2e_step():
-        q.copy_(h_q, non_blocking=True); kn.copy_(h_kn, non_blocking=True); vn.copy_(h_vn, non_blocking=True)
-        step_slots.copy_(h_slots, non_blocking=True); d_lens.copy_(h_lens, non_blocking=True); d_bt.copy_(h_bt, non_blocking=True)
-        run_step()
-        h_out.copy_(out, non_blocking=True)
+        if e2e_graph is not None:
+            e2e_graph.replay()
+        else:
+            q.copy_(h_q, non_blocking=True); kn.copy_(h_kn, non_blocking=True); vn.copy_(h_vn, non_blocking=True)
+            step_slots.copy_(h_slots, non_blocking=True); d_lens.copy_(h_lens, non_blocking=True); d_bt.copy_(h_bt, non_blocking=True)
+            run_step()
+            h_out.copy_(out, non_blocking=True)
         torch.cuda.current_stream().synchronize()   # the caller consumes the result every step
 
     for _ in range(max(3, args.warmup)):
@@ -413,10 +466,14 @@ def run_ours(args, w):
     gbs_e2e = world * step_bytes / (ms_e2e_per_step * 1e-3) / 1e9
     kern_gbs = dec_b / (kern_ms * 1e-3) / 1e9
 
+    if world > 1:
+        # every rank is past its last collective: leave without tearing NCCL down (communicators referenced by a captured
+        # graph can make destroy_process_group block); rank 0 prints first
+        dist.barrier()
+        torch.cuda.synchronize()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -436,7 +493,8 @@ def run_ours(args, w):
         "pct_of_8tbs": gbs / world / 8000.0 * 100.0, "pct_of_measured_hbm": gbs / world / peak * 100.0,
         "cuda_graph": use_graph,
         "e2e": {"value": gbs_e2e, "unit": "GB/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3)},
+                "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3),
+                "pipeline": f"one CUDA graph, {NG} layer groups: H2D / compute / D2H on three stream branches" if e2e_graph is not None else "serial copy, step, copy"},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "achieved": kern_gbs, "peak": peak, "unit": "GB/s", "frac": kern_gbs / peak,
                      "traffic": None, "kernel": ("b200attn::decode_tc_kernel" if (fp8 and Hq // Hkv <= 8) else "b200attn::decode_kernel") + " (split-KV paged flash-decoding, in-kernel merge; CUDA graph of one launch per layer cache, PDL off)",
@@ -450,12 +508,29 @@ def run_ours(args, w):
             line["roofline"]["traffic"] = json.load(f).get(args.workload)
     except Exception:  # noqa: BLE001
         pass
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
+
+
+_REAL_STDOUT = None
+
+
+def emit(text: str) -> None:
+    """The ONE JSON line goes to the real stdout; everything else a library prints there (NCCL's version banner) was
+    diverted to stderr by main()."""
+    if _REAL_STDOUT is None:
+        print(text, flush=True)
+    else:
+        os.write(_REAL_STDOUT, (text + "\n").encode())
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
