@@ -153,6 +153,10 @@ def cpu_oracle_layer(w, reps_budget_s=15.0, max_reps=5, seed=0):
     if not os.path.exists(path):
         subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
     lib = C.CDLL(path)
+    try:
+        lib.oracle_set_threads(len(os.sched_getaffinity(0)))
+    except Exception:  # noqa: BLE001
+        pass
     cores = int(lib.oracle_num_threads())
     B, L, Hq, Hkv, D, bs = w["B"], w["L"], w["Hq"], w["Hkv"], w["D"], w["bs"]
     fp8 = w["kv"] == "fp8"

@@ -72,6 +72,15 @@ static inline uint8_t e4m3_encode(float x) {
   return sign | (uint8_t)code;
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU arm asks for every core it is allowed to run on */
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int oracle_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();
