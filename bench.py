@@ -492,7 +492,7 @@ def run_ours(args, w):
         "dtype": "fp8_e4m3 KV / bf16 Q,O / tcgen05 kind::f8f6f4 (exact hi+lo e4m3 split of Q and P), fp32 accumulate" if (fp8 and Hq // Hkv <= 8) else
                  "fp8_e4m3 KV / bf16 Q,O / f16 HMMA, fp32 accumulate" if fp8 else "bf16 KV,Q,O / bf16 HMMA, fp32 accumulate",
         "data": "synthetic (N(0,1) tokens written through the KV-write path; random block permutation)",
-        "config": workload_config(args, w, ws.num_ctas),
+        "config": workload_config(args, w, ws.grid),
         "tok_s": B / (ms_per_step * 1e-3),
         "pct_of_8tbs": gbs / world / 8000.0 * 100.0, "pct_of_measured_hbm": gbs / world / peak * 100.0,
         "cuda_graph": use_graph,

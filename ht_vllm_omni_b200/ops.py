@@ -227,19 +227,38 @@ class DecodeWorkspace:
             self.num_ctas = int(num_ctas) if num_ctas else default_ctas(kv_dtype)
         if not num_ctas and kv_dtype not in _FP8_DTYPES and group_size > 8:
             self.num_ctas = max(1, self.num_ctas // 2)
+        self._fixed_grid = bool(num_ctas)   # an explicit grid (tests, sweeps) is used as given
+        self.grid = self.num_ctas           # grid of the current plan (<= num_ctas, which sizes the workspace)
         self.max_num_seqs = max_num_seqs
         self.plan = torch.zeros(plan_numel(max_num_seqs), dtype=torch.int32, device=self.device)
         self.workspace = torch.empty(workspace_numel(head_dim, self.num_ctas), dtype=torch.float32, device=self.device)
         self._no_lse = torch.empty(0, dtype=torch.float32, device=self.device)
         self._no_map = torch.empty(0, dtype=torch.int32, device=self.device)
 
+    def grid_for(self, num_seqs: int, num_q_heads: int, num_kv_heads: int) -> int:
+        """Decode grid for a batch (host-side shape arithmetic, capture-safe).  When the (sequence, kv head) pairs are few
+        enough that each can get k >= 2 CTAs, the grid is rounded down to pairs * k (if that keeps >= 80 % of the resident
+        CTAs): with equal-length sequences every CTA then owns exactly 1/k of ONE pair -- a single segment, a k-way merge
+        and no mid-range segment switch (c2: 296 -> 256 CTAs, +2.5 %; 32 x 4k: +14 %).  Ragged batches are still cut into
+        equal tile counts by the plan kernel, whatever the grid."""
+        if self._fixed_grid:
+            return self.num_ctas
+        group = max(1, num_q_heads // max(1, num_kv_heads))
+        pairs = num_seqs * num_kv_heads * (-(-group // 16))
+        if pairs > 0:
+            k = self.num_ctas // pairs
+            if k >= 2 and pairs * k * 10 >= self.num_ctas * 8:
+                return pairs * k
+        return self.num_ctas
+
     def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int) -> None:
         if seq_lens.shape[0] > self.max_num_seqs:
             raise B200AttnError(f"batch {seq_lens.shape[0]} exceeds planned max_num_seqs {self.max_num_seqs}")
-        torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.num_ctas)
+        self.grid = self.grid_for(seq_lens.shape[0], num_q_heads, num_kv_heads)
+        torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.grid)
 
     def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None,
                row_map=None, fresh_tokens: int = -1, fused_merge: bool = True) -> None:
         torch.ops.b200attn.paged_decode(query, k_cache, v_cache, block_table, seq_lens, out, self.plan, self.workspace,
-                                        k_scale, v_scale, sm_scale, self.num_ctas, self._no_lse if lse is None else lse,
+                                        k_scale, v_scale, sm_scale, self.grid, self._no_lse if lse is None else lse,
                                         self._no_map if row_map is None else row_map, fresh_tokens, fused_merge)
