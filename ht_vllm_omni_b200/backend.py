@@ -282,6 +282,28 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
                                     value[:n].view(n, self.num_kv_heads, self.head_size),
                                     k_cache, v_cache, slot_mapping[:n], k_scale, v_scale)
 
+    def fused_rope_kvcache_supported(self) -> bool:
+        """vLLM's RoPE+KV-cache fusion pass ($VLLM/compilation/passes/fusion/rope_kvcache_fusion.py:50) asks the impl; ours
+        does both in one launch (csrc/rope_kv_write.cu).  KV-sharing layers keep the unfused path (they write no cache)."""
+        return self.kv_sharing_target_layer_name is None
+
+    def do_rope_and_kv_cache_update(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                    positions: torch.Tensor, cos_sin_cache: torch.Tensor, is_neox: bool,
+                                    kv_cache: torch.Tensor, layer_slot_mapping: torch.Tensor) -> None:
+        """Replaces RotaryEmbedding.forward + reshape_and_cache_flash ($VLLM/v1/attention/backend.py:823-840; the ROCm
+        reference body is triton_attn.py:770-804).  query/key are rotated in place; the rotated key and the value go to the
+        cache.  cos_sin_cache must already be in the activation dtype (RotaryEmbedding._match_cos_sin_cache_dtype)."""
+        k_cache, v_cache = self._planes(kv_cache)
+        k_scale, v_scale = self._scales(layer, key.device)
+        n = min(layer_slot_mapping.shape[0], key.shape[0])
+        if cos_sin_cache.dtype != query.dtype:
+            cos_sin_cache = cos_sin_cache.to(query.dtype)
+        torch.ops.b200attn.rope_kv_write(query[:n].view(n, self.num_heads, self.head_size),
+                                         key[:n].view(n, self.num_kv_heads, self.head_size),
+                                         value[:n].view(n, self.num_kv_heads, self.head_size),
+                                         positions[:n].contiguous(), cos_sin_cache, bool(is_neox), k_cache, v_cache,
+                                         layer_slot_mapping[:n], k_scale, v_scale)
+
     def forward(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
                 kv_cache: torch.Tensor, attn_metadata: B200PagedAttentionMetadata, output: torch.Tensor,
                 output_scale: torch.Tensor | None = None, output_block_scale: torch.Tensor | None = None) -> torch.Tensor:

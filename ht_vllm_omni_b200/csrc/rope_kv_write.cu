@@ -1,0 +1,231 @@
+// rope_kv_write.cu — fused rotary embedding + paged KV write (the step before the path).
+//
+// Replaces, in ONE launch, the pair the reference issues per layer and step:
+//   RotaryEmbedding.forward(positions, q, k)      ($VLLM/model_executor/layers/rotary_embedding/base.py:130-180,
+//                                                   common.py:144-183; CUDA op csrc/pos_encoding_kernels.cu)
+//   reshape_and_cache_flash(k, v, ...)            ($VLLM/v1/attention/backends/flashinfer.py:1846-1855)
+// behind vLLM's hook AttentionImpl.do_rope_and_kv_cache_update ($VLLM/v1/attention/backend.py:815-840).  K is read once
+// instead of read-rotated-written-read; the rotated q and k are also stored back in place, as the unfused op does.
+//
+// Arithmetic is the reference's, operation by operation in the activation dtype (torch rounds every bf16 / fp16
+// elementary op):   o1 = rnd(rnd(x1 cos) - rnd(x2 sin)),  o2 = rnd(rnd(x2 cos) + rnd(x1 sin))
+// with (x1, x2) = the two halves of the rotary span (neox) or even / odd elements (GPT-J).  The cache bytes are then
+// those of kv_write.cu: fp32 IEEE divide by the head's scale, cvt.rn.satfinite.e4m3.
+//
+// Mapping: a (token, head) row of D elements is handled by D/16 consecutive threads, each owning two 8-element chunks:
+//   neox rotary thread j:  [8j, 8j+8) and its partners [rot/2 + 8j, +8)          (cos/sin index 8j..8j+7)
+//   GPT-J rotary thread j: [16j, 16j+16) = 8 adjacent pairs                      (cos/sin index 8j..8j+7)
+//   pass-through thread (elements >= rotary_dim, and every V row): 16 contiguous elements, no rotation.
+// All global accesses are 16-byte vectors (8-byte for an fp8 cache chunk).
+#include "common.cuh"
+
+namespace b200attn {
+
+struct RopeKvParams {
+  void* query;
+  void* key;
+  const void* value;
+  int64_t q_stride_t, q_stride_h, key_stride_t, key_stride_h, value_stride_t, value_stride_h;
+  const int64_t* positions;
+  const void* cos_sin;   // [max_pos][rot]: cos (rot/2) then sin (rot/2), activation dtype
+  void* k_cache;
+  void* v_cache;
+  int64_t stride_block, stride_slot, stride_head;
+  const int64_t* slot_mapping;
+  const float* k_scale;
+  const float* v_scale;
+  int scale_stride;
+  int T, Hq, Hkv, D, rot, block_size, is_neox;
+};
+
+template <int DT>
+__device__ __forceinline__ float rnd(float x) {
+  using E = Elem<DT>;
+  return E::to_float(E::from_float(x));
+}
+
+template <int DT>
+__device__ __forceinline__ void load8(const void* base, int64_t off, float (&f)[8]) {
+  using E = Elem<DT>;
+  const uint4 raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const typename E::type*>(base) + off);
+  const typename E::type* e = reinterpret_cast<const typename E::type*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) f[i] = E::to_float(e[i]);
+}
+
+template <int DT>
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  using E = Elem<DT>;
+  uint4 raw;
+  typename E::type* e = reinterpret_cast<typename E::type*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) e[i] = E::from_float(f[i]);
+  return raw;
+}
+
+__device__ __forceinline__ uint2 quant8(const float (&f)[8], float scale) {
+  uint32_t w[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float2 lo = make_float2(__fdiv_rn(f[4 * i + 0], scale), __fdiv_rn(f[4 * i + 1], scale));
+    const float2 hi = make_float2(__fdiv_rn(f[4 * i + 2], scale), __fdiv_rn(f[4 * i + 3], scale));
+    w[i] = (uint32_t)__nv_cvt_float2_to_fp8x2(lo, __NV_SATFINITE, __NV_E4M3) |
+           ((uint32_t)__nv_cvt_float2_to_fp8x2(hi, __NV_SATFINITE, __NV_E4M3) << 16);
+  }
+  return make_uint2(w[0], w[1]);
+}
+
+template <int DT, bool FP8>
+__global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p) {
+  using E = Elem<DT>;
+  const int lanes = p.D >> 4;
+  const int units = p.Hq + 2 * p.Hkv;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t row = gid / lanes;
+  const int j = (int)(gid - row * lanes);
+  pdl_launch_dependents();
+  pdl_wait();
+  if (row >= (int64_t)p.T * units) return;
+  const int t = (int)(row / units);
+  const int u = (int)(row - (int64_t)t * units);
+  const int kind = u < p.Hq ? 0 : (u < p.Hq + p.Hkv ? 1 : 2);   // q, k, v
+  const int h = kind == 0 ? u : (kind == 1 ? u - p.Hq : u - p.Hq - p.Hkv);
+  const int64_t slot = p.slot_mapping[t];
+  if (kind == 2 && slot < 0) return;
+
+  const int half = p.rot >> 1;
+  const bool rotary = kind != 2 && j < (p.rot >> 4);
+  int a0, a1;
+  if (rotary && p.is_neox) { a0 = 8 * j; a1 = half + 8 * j; }
+  else if (rotary) { a0 = 16 * j; a1 = a0 + 8; }
+  else { a0 = (kind == 2 ? 0 : p.rot) + 16 * (j - (kind == 2 ? 0 : (p.rot >> 4))); a1 = a0 + 8; }
+  if (kind == 0 && !rotary) return;   // q elements beyond the rotary span stay as they are
+
+  void* base = kind == 0 ? p.query : (kind == 1 ? p.key : const_cast<void*>(p.value));
+  const int64_t roff = kind == 0 ? (int64_t)t * p.q_stride_t + (int64_t)h * p.q_stride_h
+                     : kind == 1 ? (int64_t)t * p.key_stride_t + (int64_t)h * p.key_stride_h
+                                 : (int64_t)t * p.value_stride_t + (int64_t)h * p.value_stride_h;
+  float c0[8], c1[8];
+  load8<DT>(base, roff + a0, c0);
+  load8<DT>(base, roff + a1, c1);
+
+  if (rotary) {
+    const int64_t pos = p.positions[t];
+    float cs[8], sn[8];
+    load8<DT>(p.cos_sin, pos * p.rot + 8 * j, cs);
+    load8<DT>(p.cos_sin, pos * p.rot + half + 8 * j, sn);
+    if (p.is_neox) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float x1 = c0[i], x2 = c1[i];
+        c0[i] = rnd<DT>(rnd<DT>(x1 * cs[i]) - rnd<DT>(x2 * sn[i]));
+        c1[i] = rnd<DT>(rnd<DT>(x2 * cs[i]) + rnd<DT>(x1 * sn[i]));
+      }
+    } else {
+      float e[16];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { e[i] = c0[i]; e[8 + i] = c1[i]; }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float x1 = e[2 * i], x2 = e[2 * i + 1];
+        e[2 * i] = rnd<DT>(rnd<DT>(x1 * cs[i]) - rnd<DT>(x2 * sn[i]));
+        e[2 * i + 1] = rnd<DT>(rnd<DT>(x2 * cs[i]) + rnd<DT>(x1 * sn[i]));
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { c0[i] = e[i]; c1[i] = e[8 + i]; }
+    }
+    // rotated q / k go back in place, like torch.ops._C.rotary_embedding
+    typename E::type* dst = reinterpret_cast<typename E::type*>(base) + roff;
+    *reinterpret_cast<uint4*>(dst + a0) = pack8<DT>(c0);
+    *reinterpret_cast<uint4*>(dst + a1) = pack8<DT>(c1);
+  }
+  if (kind == 0 || slot < 0) return;
+
+  const int64_t blk = slot / p.block_size;
+  const int64_t off = slot - blk * p.block_size;
+  const int64_t dst_off = blk * p.stride_block + off * p.stride_slot + (int64_t)h * p.stride_head;
+  if constexpr (FP8) {
+    const float scale = __ldg((kind == 1 ? p.k_scale : p.v_scale) + (int64_t)h * p.scale_stride);
+    uint8_t* dst = reinterpret_cast<uint8_t*>(kind == 1 ? p.k_cache : p.v_cache) + dst_off;
+    *reinterpret_cast<uint2*>(dst + a0) = quant8(c0, scale);
+    *reinterpret_cast<uint2*>(dst + a1) = quant8(c1, scale);
+  } else {
+    typename E::type* dst = reinterpret_cast<typename E::type*>(kind == 1 ? p.k_cache : p.v_cache) + dst_off;
+    *reinterpret_cast<uint4*>(dst + a0) = pack8<DT>(c0);
+    *reinterpret_cast<uint4*>(dst + a1) = pack8<DT>(c1);
+  }
+}
+
+int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
+
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads, void* key,
+                                      const void* value, int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t,
+                                      int64_t value_stride_h, const int64_t* positions, const void* cos_sin_cache,
+                                      int32_t rotary_dim, int32_t is_neox, void* k_cache, void* v_cache, int64_t stride_block,
+                                      int64_t stride_slot, int64_t stride_head, const int64_t* slot_mapping,
+                                      int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                                      int32_t in_dtype, int32_t kv_dtype, const float* k_scale, const float* v_scale,
+                                      int32_t scale_stride, void* stream) {
+  if (num_tokens == 0) return B200ATTN_OK;
+  if (!query || !key || !value || !positions || !cos_sin_cache || !k_cache || !v_cache || !slot_mapping) {
+    set_error("rope_kv_write: null pointer argument");
+    return B200ATTN_EINVAL;
+  }
+  if (num_tokens < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || block_size <= 0 || head_dim <= 0 || (head_dim % 16) != 0) {
+    set_error("rope_kv_write: bad shape T=%d Hq=%d Hkv=%d D=%d block_size=%d (D must be a multiple of 16)", num_tokens,
+              num_q_heads, num_kv_heads, head_dim, block_size);
+    return B200ATTN_EINVAL;
+  }
+  if (rotary_dim <= 0 || rotary_dim > head_dim || (rotary_dim % 16) != 0) {
+    set_error("rope_kv_write: rotary_dim %d must be a positive multiple of 16 and <= head_dim %d", rotary_dim, head_dim);
+    return B200ATTN_EINVAL;
+  }
+  if (in_dtype != B200ATTN_BF16 && in_dtype != B200ATTN_FP16) {
+    set_error("rope_kv_write: q/k/v dtype must be bf16 or fp16 (got %d)", in_dtype);
+    return B200ATTN_EINVAL;
+  }
+  const bool fp8 = kv_dtype == B200ATTN_FP8_E4M3;
+  if (!fp8 && kv_dtype != in_dtype) {
+    set_error("rope_kv_write: 16-bit cache dtype (%d) must equal q/k/v dtype (%d)", kv_dtype, in_dtype);
+    return B200ATTN_EINVAL;
+  }
+  if (fp8 && (!k_scale || !v_scale)) {
+    set_error("rope_kv_write: fp8 cache needs k_scale / v_scale");
+    return B200ATTN_EINVAL;
+  }
+  const int64_t es_out = fp8 ? 1 : 2;
+  auto mis = [](const void* p, int64_t a) { return (reinterpret_cast<uintptr_t>(p) % a) != 0; };
+  if (mis(query, 16) || mis(key, 16) || mis(value, 16) || mis(cos_sin_cache, 16) || mis(k_cache, 16) || mis(v_cache, 16) ||
+      (q_stride_t % 8) || (q_stride_h % 8) || (key_stride_t % 8) || (key_stride_h % 8) || (value_stride_t % 8) ||
+      (value_stride_h % 8) || ((stride_block * es_out) % 16) || ((stride_slot * es_out) % 16) ||
+      ((stride_head * es_out) % 16)) {
+    set_error("rope_kv_write: pointers and strides must be 16-byte aligned");
+    return B200ATTN_EINVAL;
+  }
+  RopeKvParams p;
+  p.query = query; p.key = key; p.value = value;
+  p.q_stride_t = q_stride_t; p.q_stride_h = q_stride_h;
+  p.key_stride_t = key_stride_t; p.key_stride_h = key_stride_h;
+  p.value_stride_t = value_stride_t; p.value_stride_h = value_stride_h;
+  p.positions = positions; p.cos_sin = cos_sin_cache;
+  p.k_cache = k_cache; p.v_cache = v_cache;
+  p.stride_block = stride_block; p.stride_slot = stride_slot; p.stride_head = stride_head;
+  p.slot_mapping = slot_mapping; p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;
+  p.T = num_tokens; p.Hq = num_q_heads; p.Hkv = num_kv_heads; p.D = head_dim; p.rot = rotary_dim;
+  p.block_size = block_size; p.is_neox = is_neox ? 1 : 0;
+
+  const int64_t threads = (int64_t)num_tokens * (num_q_heads + 2 * num_kv_heads) * (head_dim / 16);
+  const int block = 256;
+  const int64_t grid = (threads + block - 1) / block;
+  const void* fn;
+  if (fp8)
+    fn = in_dtype == B200ATTN_BF16 ? (const void*)rope_kv_write_kernel<B200ATTN_BF16, true> : (const void*)rope_kv_write_kernel<B200ATTN_FP16, true>;
+  else
+    fn = in_dtype == B200ATTN_BF16 ? (const void*)rope_kv_write_kernel<B200ATTN_BF16, false> : (const void*)rope_kv_write_kernel<B200ATTN_FP16, false>;
+  void* args[] = {&p};
+  return launch_with_pdl(fn, dim3((unsigned)grid), dim3(block), 0, static_cast<cudaStream_t>(stream), args);
+}

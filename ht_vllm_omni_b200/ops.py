@@ -105,6 +105,44 @@ def _(key, value, k_cache, v_cache, slot_mapping, k_scale, v_scale) -> None:
 
 
 # ------------------------------------------------------------------------------------------------
+# rope_kv_write: rotary embedding of q / k in place + KV write, one launch (do_rope_and_kv_cache_update)
+# ------------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200attn::rope_kv_write", mutates_args=("query", "key", "k_cache", "v_cache"), device_types="cuda")
+def rope_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, positions: torch.Tensor,
+                  cos_sin_cache: torch.Tensor, is_neox: bool, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                  slot_mapping: torch.Tensor, k_scale: torch.Tensor, v_scale: torch.Tensor) -> None:
+    """query [T, Hq, D], key / value [T, Hkv, D] (head_dim contiguous), positions int64 [T], cos_sin_cache
+    [max_pos, rotary_dim] in the activation dtype (vLLM's RotaryEmbedding.cos_sin_cache after _match_cos_sin_cache_dtype)."""
+    _require_cuda(query, key, value, positions, cos_sin_cache, k_cache, v_cache, slot_mapping)
+    lib = load_library()
+    T = slot_mapping.shape[0]
+    if T == 0:
+        return
+    if query.dim() != 3 or key.dim() != 3 or value.shape != key.shape or query.stride(2) != 1 or key.stride(2) != 1 or value.stride(2) != 1:
+        raise B200AttnError("query/key/value must be [T, H, D] with contiguous head_dim")
+    if query.shape[0] < T or key.shape[0] < T or positions.shape[0] < T:
+        raise B200AttnError("query/key/value/positions must cover every slot_mapping entry")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous() or positions.dtype != torch.int64 or not positions.is_contiguous():
+        raise B200AttnError("slot_mapping and positions must be contiguous int64")
+    if cos_sin_cache.dtype != query.dtype or key.dtype != query.dtype or value.dtype != query.dtype or not cos_sin_cache.is_contiguous():
+        raise B200AttnError("cos_sin_cache, key and value must have the query dtype (cos_sin_cache contiguous)")
+    Hq, Hkv, D = query.shape[1], key.shape[1], key.shape[2]
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    kvdt = _dt(k_cache)
+    sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
+    check(lib.b200attn_rope_kv_write(
+        query.data_ptr(), query.stride(0), query.stride(1), Hq, key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1),
+        value.stride(0), value.stride(1), positions.data_ptr(), cos_sin_cache.data_ptr(), cos_sin_cache.shape[1], int(bool(is_neox)),
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, slot_mapping.data_ptr(), T, Hkv, D, k_cache.shape[1],
+        _dt(query), kvdt, k_scale.data_ptr(), v_scale.data_ptr(), sstride, _stream(query)), "b200attn_rope_kv_write")
+
+
+@rope_kv_write.register_fake
+def _(query, key, value, positions, cos_sin_cache, is_neox, k_cache, v_cache, slot_mapping, k_scale, v_scale) -> None:
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
 # decode_plan (once per step) and paged_decode (= split-KV decode kernel + merge kernel)
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("b200attn::decode_plan", mutates_args=("plan",), device_types="cuda")

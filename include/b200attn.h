@@ -85,6 +85,33 @@ B200ATTN_API int b200attn_kv_write(const void* key, const void* value,
                       void* stream);
 
 /*
+ * Kernel 1b -- fused rotary embedding + KV write (the step before the path).
+ * Replaces, in one launch: RotaryEmbedding.forward(positions, q, k)
+ *   ($VLLM/model_executor/layers/rotary_embedding/base.py:130-180, common.py:144-183; torch.ops._C.rotary_embedding)
+ *   followed by reshape_and_cache_flash, i.e. the body of AttentionImpl.do_rope_and_kv_cache_update
+ *   ($VLLM/v1/attention/backend.py:815-840; call order $VLLM/model_executor/models/qwen3.py:153-160).
+ *
+ * query [T][Hq][D] and key [T][Hkv][D] are rotated IN PLACE over their first rotary_dim elements (neox: halves of the span
+ * are partners; otherwise even/odd elements), every elementary operation rounded to the activation dtype exactly as torch
+ * does:  o1 = rnd(rnd(x1*cos) - rnd(x2*sin)), o2 = rnd(rnd(x2*cos) + rnd(x1*sin)).  cos_sin_cache is vLLM's
+ * [max_position][rotary_dim] table (cos half, then sin half) in the activation dtype.  The rotated key and the value are
+ * then written to the cache with b200attn_kv_write's semantics (slot < 0: no cache write; the rotation still happens).
+ * rotary_dim must be a multiple of 16.
+ */
+B200ATTN_API int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads,
+                           void* key, const void* value,
+                           int64_t key_stride_t, int64_t key_stride_h,
+                           int64_t value_stride_t, int64_t value_stride_h,
+                           const int64_t* positions, const void* cos_sin_cache, int32_t rotary_dim, int32_t is_neox,
+                           void* k_cache, void* v_cache,
+                           int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                           const int64_t* slot_mapping, int32_t num_tokens,
+                           int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                           int32_t in_dtype, int32_t kv_dtype,
+                           const float* k_scale, const float* v_scale, int32_t scale_stride,
+                           void* stream);
+
+/*
  * Split-KV work plan (once per decode step, shared by all layers).
  * Replaces: the per-step planning in AttentionMetadataBuilder.build
  *   ($VLLM/v1/attention/backends/flashinfer.py:886-1248 `plan`, triton_attn.py:216-268).

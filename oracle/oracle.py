@@ -123,6 +123,56 @@ def kv_write_ref(key, value, k_cache, v_cache, slot_mapping, k_scale=None, v_sca
 
 
 # ------------------------------------------------------------------------------------------------
+# RoPE + KV write  (SURVEY.md 8(f) rank 1: AttentionImpl.do_rope_and_kv_cache_update, $VLLM/v1/attention/backend.py:815-840)
+# Unfused reference = RotaryEmbedding.forward ($VLLM/model_executor/layers/rotary_embedding/base.py:130-180,
+# common.py:144-183 ApplyRotaryEmb.forward_static; csrc/pos_encoding_kernels.cu computes the same scalar_t arithmetic)
+# followed by reshape_and_cache_flash.
+# ------------------------------------------------------------------------------------------------
+
+
+def rope_cos_sin_cache(rotary_dim: int, max_pos: int, base: float, act: str) -> np.ndarray:
+    """[max_pos, rotary_dim] = cat(cos, sin) of outer(t, base^(-2i/rotary_dim)), rounded to the activation dtype
+    (base.py:_compute_inv_freq / _compute_cos_sin_cache + _match_cos_sin_cache_dtype)."""
+    inv_freq = (1.0 / (np.float32(base) ** (np.arange(0, rotary_dim, 2, dtype=np.float32) / np.float32(rotary_dim)))).astype(np.float32)
+    freqs = np.outer(np.arange(max_pos, dtype=np.float32), inv_freq).astype(np.float32)
+    return act_round(np.concatenate([np.cos(freqs), np.sin(freqs)], axis=-1).astype(np.float32), act)
+
+
+def rope_ref(x, positions, cos_sin_cache, rotary_dim: int, is_neox: bool, act: str) -> np.ndarray:
+    """x float32 [T, H, D] holding activation-dtype values; returns the rotated copy.  Every elementary operation is
+    rounded to the activation dtype, as torch does for bf16/fp16 tensors (common.py:173-174):
+        o1 = rnd(rnd(x1 * cos) - rnd(x2 * sin));  o2 = rnd(rnd(x2 * cos) + rnd(x1 * sin))
+    neox: (x1, x2) = halves of the rotary span; GPT-J: even / odd elements (common.py:167-171)."""
+    x = np.asarray(x, dtype=np.float32)
+    out = x.copy()
+    half = rotary_dim // 2
+    cs = np.asarray(cos_sin_cache, dtype=np.float32)[np.asarray(positions, dtype=np.int64)]   # [T, rotary_dim]
+    cos, sin = cs[:, None, :half], cs[:, None, half:]
+    rot = x[..., :rotary_dim]
+    if is_neox:
+        x1, x2 = rot[..., :half], rot[..., half:]
+    else:
+        x1, x2 = rot[..., 0::2], rot[..., 1::2]
+    r = lambda a: act_round(a, act)  # noqa: E731
+    o1 = r(r(x1 * cos) - r(x2 * sin))
+    o2 = r(r(x2 * cos) + r(x1 * sin))
+    if is_neox:
+        out[..., :half], out[..., half:rotary_dim] = o1, o2
+    else:
+        out[..., 0:rotary_dim:2], out[..., 1:rotary_dim:2] = o1, o2
+    return out
+
+
+def rope_kv_write_ref(query, key, value, positions, cos_sin_cache, rotary_dim, is_neox, act, k_cache, v_cache, slot_mapping,
+                      k_scale=None, v_scale=None, fp8=False):
+    """Returns (q', k'); k' and value are written to the cache exactly as kv_write_ref does."""
+    q2 = rope_ref(query, positions, cos_sin_cache, rotary_dim, is_neox, act)
+    k2 = rope_ref(key, positions, cos_sin_cache, rotary_dim, is_neox, act)
+    kv_write_ref(k2, value, k_cache, v_cache, slot_mapping, k_scale, v_scale, fp8)
+    return q2, k2
+
+
+# ------------------------------------------------------------------------------------------------
 # paged decode attention (q_len = 1)
 # ------------------------------------------------------------------------------------------------
 
