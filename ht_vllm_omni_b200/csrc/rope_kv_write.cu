@@ -7,8 +7,8 @@
 // behind vLLM's hook AttentionImpl.do_rope_and_kv_cache_update ($VLLM/v1/attention/backend.py:815-840).  K is read once
 // instead of read-rotated-written-read; the rotated q and k are also stored back in place, as the unfused op does.
 //
-// Arithmetic is the reference's, operation by operation in the activation dtype (torch rounds every bf16 / fp16
-// elementary op):   o1 = rnd(rnd(x1 cos) - rnd(x2 sin)),  o2 = rnd(rnd(x2 cos) + rnd(x1 sin))
+// Arithmetic is the reference's:  o1 = rnd(x1 cos - x2 sin),  o2 = rnd(x2 cos + x1 sin)  in fp32 with one rounding to the
+// activation dtype (the compiled CUDA op), or with every elementary op rounded (B200ATTN_ROPE_ROUND_EACH_OP, torch-native),
 // with (x1, x2) = the two halves of the rotary span (neox) or even / odd elements (GPT-J).  The cache bytes are then
 // those of kv_write.cu: fp32 IEEE divide by the head's scale, cvt.rn.satfinite.e4m3.
 //
@@ -35,13 +35,26 @@ struct RopeKvParams {
   const float* k_scale;
   const float* v_scale;
   int scale_stride;
-  int T, Hq, Hkv, D, rot, block_size, is_neox;
+  int T, Hq, Hkv, D, rot, block_size, is_neox, each_op;
 };
 
 template <int DT>
 __device__ __forceinline__ float rnd(float x) {
   using E = Elem<DT>;
   return E::to_float(E::from_float(x));
+}
+
+// The two roundings the reference has: its compiled CUDA op (csrc/pos_encoding_kernels.cu, what a GPU run executes)
+// computes in fp32 and rounds once -- measured on the box, tests/tools/rope_probe.py: 0 mismatches in 524288 elements;
+// products of two 16-bit floats are exact in fp32, so FMA contraction cannot change the result -- while forward_native
+// (torch bf16 / fp16 tensor arithmetic) rounds every elementary operation.
+template <int DT>
+__device__ __forceinline__ float rot1(float x1, float x2, float c, float s, int each_op) {
+  return each_op ? rnd<DT>(rnd<DT>(x1 * c) - rnd<DT>(x2 * s)) : rnd<DT>(x1 * c - x2 * s);
+}
+template <int DT>
+__device__ __forceinline__ float rot2(float x1, float x2, float c, float s, int each_op) {
+  return each_op ? rnd<DT>(rnd<DT>(x2 * c) + rnd<DT>(x1 * s)) : rnd<DT>(x2 * c + x1 * s);
 }
 
 template <int DT>
@@ -118,8 +131,8 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float x1 = c0[i], x2 = c1[i];
-        c0[i] = rnd<DT>(rnd<DT>(x1 * cs[i]) - rnd<DT>(x2 * sn[i]));
-        c1[i] = rnd<DT>(rnd<DT>(x2 * cs[i]) + rnd<DT>(x1 * sn[i]));
+        c0[i] = rot1<DT>(x1, x2, cs[i], sn[i], p.each_op);
+        c1[i] = rot2<DT>(x1, x2, cs[i], sn[i], p.each_op);
       }
     } else {
       float e[16];
@@ -128,8 +141,8 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float x1 = e[2 * i], x2 = e[2 * i + 1];
-        e[2 * i] = rnd<DT>(rnd<DT>(x1 * cs[i]) - rnd<DT>(x2 * sn[i]));
-        e[2 * i + 1] = rnd<DT>(rnd<DT>(x2 * cs[i]) + rnd<DT>(x1 * sn[i]));
+        e[2 * i] = rot1<DT>(x1, x2, cs[i], sn[i], p.each_op);
+        e[2 * i + 1] = rot2<DT>(x1, x2, cs[i], sn[i], p.each_op);
       }
 #pragma unroll
       for (int i = 0; i < 8; ++i) { c0[i] = e[i]; c1[i] = e[8 + i]; }
@@ -165,7 +178,7 @@ using namespace b200attn;
 extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads, void* key,
                                       const void* value, int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t,
                                       int64_t value_stride_h, const int64_t* positions, const void* cos_sin_cache,
-                                      int32_t rotary_dim, int32_t is_neox, void* k_cache, void* v_cache, int64_t stride_block,
+                                      int32_t rotary_dim, int32_t rope_flags, void* k_cache, void* v_cache, int64_t stride_block,
                                       int64_t stride_slot, int64_t stride_head, const int64_t* slot_mapping,
                                       int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
                                       int32_t in_dtype, int32_t kv_dtype, const float* k_scale, const float* v_scale,
@@ -216,7 +229,9 @@ extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q
   p.stride_block = stride_block; p.stride_slot = stride_slot; p.stride_head = stride_head;
   p.slot_mapping = slot_mapping; p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;
   p.T = num_tokens; p.Hq = num_q_heads; p.Hkv = num_kv_heads; p.D = head_dim; p.rot = rotary_dim;
-  p.block_size = block_size; p.is_neox = is_neox ? 1 : 0;
+  p.block_size = block_size;
+  p.is_neox = (rope_flags & B200ATTN_ROPE_NEOX) ? 1 : 0;
+  p.each_op = (rope_flags & B200ATTN_ROPE_ROUND_EACH_OP) ? 1 : 0;
 
   const int64_t threads = (int64_t)num_tokens * (num_q_heads + 2 * num_kv_heads) * (head_dim / 16);
   const int block = 256;

@@ -110,8 +110,9 @@ def _(key, value, k_cache, v_cache, slot_mapping, k_scale, v_scale) -> None:
 @torch.library.custom_op("b200attn::rope_kv_write", mutates_args=("query", "key", "k_cache", "v_cache"), device_types="cuda")
 def rope_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, positions: torch.Tensor,
                   cos_sin_cache: torch.Tensor, is_neox: bool, k_cache: torch.Tensor, v_cache: torch.Tensor,
-                  slot_mapping: torch.Tensor, k_scale: torch.Tensor, v_scale: torch.Tensor) -> None:
-    """query [T, Hq, D], key / value [T, Hkv, D] (head_dim contiguous), positions int64 [T], cos_sin_cache
+                  slot_mapping: torch.Tensor, k_scale: torch.Tensor, v_scale: torch.Tensor, round_each_op: bool = False) -> None:
+    """`round_each_op`: torch-native rounding (forward_native) instead of the compiled op's fp32 arithmetic.
+    query [T, Hq, D], key / value [T, Hkv, D] (head_dim contiguous), positions int64 [T], cos_sin_cache
     [max_pos, rotary_dim] in the activation dtype (vLLM's RotaryEmbedding.cos_sin_cache after _match_cos_sin_cache_dtype)."""
     _require_cuda(query, key, value, positions, cos_sin_cache, k_cache, v_cache, slot_mapping)
     lib = load_library()
@@ -132,13 +133,13 @@ def rope_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, p
     sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
     check(lib.b200attn_rope_kv_write(
         query.data_ptr(), query.stride(0), query.stride(1), Hq, key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1),
-        value.stride(0), value.stride(1), positions.data_ptr(), cos_sin_cache.data_ptr(), cos_sin_cache.shape[1], int(bool(is_neox)),
+        value.stride(0), value.stride(1), positions.data_ptr(), cos_sin_cache.data_ptr(), cos_sin_cache.shape[1], (1 if is_neox else 0) | (2 if round_each_op else 0),
         k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, slot_mapping.data_ptr(), T, Hkv, D, k_cache.shape[1],
         _dt(query), kvdt, k_scale.data_ptr(), v_scale.data_ptr(), sstride, _stream(query)), "b200attn_rope_kv_write")
 
 
 @rope_kv_write.register_fake
-def _(query, key, value, positions, cos_sin_cache, is_neox, k_cache, v_cache, slot_mapping, k_scale, v_scale) -> None:
+def _(query, key, value, positions, cos_sin_cache, is_neox, k_cache, v_cache, slot_mapping, k_scale, v_scale, round_each_op=False) -> None:
     return None
 
 

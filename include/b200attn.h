@@ -48,6 +48,10 @@ extern "C" {
 #define B200ATTN_ENOSPACE (-3) /* plan or workspace buffer too small */
 
 /* b200attn_decode flags */
+/* b200attn_rope_kv_write flags */
+#define B200ATTN_ROPE_NEOX 1           /* partners are the halves of the rotary span (else even / odd elements) */
+#define B200ATTN_ROPE_ROUND_EACH_OP 2  /* torch-native rounding of every elementary op (default: fp32, one rounding) */
+
 #define B200ATTN_DECODE_FUSED_MERGE 1 /* merge split-KV partials inside the decode kernel (no b200attn_merge call) */
 
 /* geometry constants the host side needs */
@@ -92,8 +96,10 @@ B200ATTN_API int b200attn_kv_write(const void* key, const void* value,
  *   ($VLLM/v1/attention/backend.py:815-840; call order $VLLM/model_executor/models/qwen3.py:153-160).
  *
  * query [T][Hq][D] and key [T][Hkv][D] are rotated IN PLACE over their first rotary_dim elements (neox: halves of the span
- * are partners; otherwise even/odd elements), every elementary operation rounded to the activation dtype exactly as torch
- * does:  o1 = rnd(rnd(x1*cos) - rnd(x2*sin)), o2 = rnd(rnd(x2*cos) + rnd(x1*sin)).  cos_sin_cache is vLLM's
+ * are partners, B200ATTN_ROPE_NEOX; otherwise even/odd elements):  o1 = rnd(x1*cos - x2*sin), o2 = rnd(x2*cos + x1*sin),
+ * computed in fp32 and rounded once to the activation dtype -- bit-identical to the compiled op a GPU run of the reference
+ * executes.  With B200ATTN_ROPE_ROUND_EACH_OP every elementary operation is rounded instead, bit-identical to
+ * RotaryEmbedding.forward_native (torch bf16/fp16 tensor arithmetic).  cos_sin_cache is vLLM's
  * [max_position][rotary_dim] table (cos half, then sin half) in the activation dtype.  The rotated key and the value are
  * then written to the cache with b200attn_kv_write's semantics (slot < 0: no cache write; the rotation still happens).
  * rotary_dim must be a multiple of 16.
@@ -102,7 +108,7 @@ B200ATTN_API int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t
                            void* key, const void* value,
                            int64_t key_stride_t, int64_t key_stride_h,
                            int64_t value_stride_t, int64_t value_stride_h,
-                           const int64_t* positions, const void* cos_sin_cache, int32_t rotary_dim, int32_t is_neox,
+                           const int64_t* positions, const void* cos_sin_cache, int32_t rotary_dim, int32_t rope_flags,
                            void* k_cache, void* v_cache,
                            int64_t stride_block, int64_t stride_slot, int64_t stride_head,
                            const int64_t* slot_mapping, int32_t num_tokens,

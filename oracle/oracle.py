@@ -138,9 +138,12 @@ def rope_cos_sin_cache(rotary_dim: int, max_pos: int, base: float, act: str) -> 
     return act_round(np.concatenate([np.cos(freqs), np.sin(freqs)], axis=-1).astype(np.float32), act)
 
 
-def rope_ref(x, positions, cos_sin_cache, rotary_dim: int, is_neox: bool, act: str) -> np.ndarray:
-    """x float32 [T, H, D] holding activation-dtype values; returns the rotated copy.  Every elementary operation is
-    rounded to the activation dtype, as torch does for bf16/fp16 tensors (common.py:173-174):
+def rope_ref(x, positions, cos_sin_cache, rotary_dim: int, is_neox: bool, act: str, each_op: bool = False) -> np.ndarray:
+    """x float32 [T, H, D] holding activation-dtype values; returns the rotated copy.
+    each_op=False: the compiled CUDA op's arithmetic (csrc/pos_encoding_kernels.cu) -- fp32, one rounding; pinned on the box
+    against torch.ops._C.rotary_embedding (tests/test_gpu_vs_vllm.py, tests/tools/rope_probe.py).
+    each_op=True: every elementary operation rounded to the activation dtype, as torch does for bf16/fp16 tensors
+    (forward_native, common.py:173-174; pinned by tests/golden/vllm_rope_native.npz):
         o1 = rnd(rnd(x1 * cos) - rnd(x2 * sin));  o2 = rnd(rnd(x2 * cos) + rnd(x1 * sin))
     neox: (x1, x2) = halves of the rotary span; GPT-J: even / odd elements (common.py:167-171)."""
     x = np.asarray(x, dtype=np.float32)
@@ -154,8 +157,12 @@ def rope_ref(x, positions, cos_sin_cache, rotary_dim: int, is_neox: bool, act: s
     else:
         x1, x2 = rot[..., 0::2], rot[..., 1::2]
     r = lambda a: act_round(a, act)  # noqa: E731
-    o1 = r(r(x1 * cos) - r(x2 * sin))
-    o2 = r(r(x2 * cos) + r(x1 * sin))
+    if each_op:
+        o1 = r(r(x1 * cos) - r(x2 * sin))
+        o2 = r(r(x2 * cos) + r(x1 * sin))
+    else:   # products of two 16-bit floats are exact in float32
+        o1 = r((x1 * cos).astype(np.float32) - (x2 * sin).astype(np.float32))
+        o2 = r((x2 * cos).astype(np.float32) + (x1 * sin).astype(np.float32))
     if is_neox:
         out[..., :half], out[..., half:rotary_dim] = o1, o2
     else:
@@ -164,10 +171,10 @@ def rope_ref(x, positions, cos_sin_cache, rotary_dim: int, is_neox: bool, act: s
 
 
 def rope_kv_write_ref(query, key, value, positions, cos_sin_cache, rotary_dim, is_neox, act, k_cache, v_cache, slot_mapping,
-                      k_scale=None, v_scale=None, fp8=False):
+                      k_scale=None, v_scale=None, fp8=False, each_op=False):
     """Returns (q', k'); k' and value are written to the cache exactly as kv_write_ref does."""
-    q2 = rope_ref(query, positions, cos_sin_cache, rotary_dim, is_neox, act)
-    k2 = rope_ref(key, positions, cos_sin_cache, rotary_dim, is_neox, act)
+    q2 = rope_ref(query, positions, cos_sin_cache, rotary_dim, is_neox, act, each_op)
+    k2 = rope_ref(key, positions, cos_sin_cache, rotary_dim, is_neox, act, each_op)
     kv_write_ref(k2, value, k_cache, v_cache, slot_mapping, k_scale, v_scale, fp8)
     return q2, k2
 

@@ -90,3 +90,47 @@ def test_decode_vs_vllm_triton_unified_attention(vllm_ops, kv, tol, segs):
     ulp = np.maximum(np.abs(want), 2.0 ** -14) * 2.0 ** -7     # both sides are rounded to bf16
     err = np.abs(got - want)
     assert np.all(err <= tol + ulp), f"max |ours - vLLM| = {err.max():.3e}"
+
+
+@pytest.mark.parametrize("act,neox,kv", [("bf16", True, "fp8"), ("bf16", False, "bf16"), ("fp16", True, "fp8")])
+def test_rope_kv_write_bit_exact_vs_vllm_cuda_ops(vllm_ops, act, neox, kv):
+    """Fused launch vs the reference's two compiled ops: torch.ops._C.rotary_embedding ($VLLM/_custom_ops.py rotary_embedding,
+    csrc/pos_encoding_kernels.cu) then reshape_and_cache_flash -- rotated q / k and the cache bytes, bit for bit."""
+    cops, _, _ = vllm_ops
+    if not hasattr(cops, "rotary_embedding"):
+        pytest.skip("vllm._custom_ops.rotary_embedding missing from this wheel")
+    import ht_vllm_omni_b200.ops  # noqa: F401
+    from oracle import oracle as O
+
+    dt = {"bf16": torch.bfloat16, "fp16": torch.float16}[act]
+    T, Hq, Hkv, D, bs, nb, max_pos = 200, 16, 2, 128, 16, 16, 8192
+    gen = torch.Generator().manual_seed(21)
+    q = torch.randn(T, Hq * D, generator=gen).to(dt).cuda()
+    k = torch.randn(T, Hkv * D, generator=gen).to(dt).cuda()
+    v = torch.randn(T, Hkv * D, generator=gen).to(dt).cuda()
+    cache = torch.from_numpy(O.rope_cos_sin_cache(D, max_pos, 1e6, act)).to(dt).cuda()
+    pos = torch.randint(0, max_pos, (T,), generator=gen, dtype=torch.int64).cuda()
+    slots = torch.randperm(nb * bs, generator=gen)[:T].to(torch.int64).cuda()
+    slots[9] = -1
+    ks = torch.full((1,), 0.03, device="cuda"); vs = torch.full((1,), 0.02, device="cuda")
+    fp8 = kv == "fp8"
+    mine = torch.zeros((nb, 2, bs, Hkv, D), dtype=torch.uint8 if fp8 else dt, device="cuda")
+    ref = torch.zeros_like(mine)
+    mk, mv = mine.unbind(1)
+    rk, rv = ref.unbind(1)
+    q1, k1 = q.clone(), k.clone()
+    torch.ops.b200attn.rope_kv_write(q1.view(T, Hq, D), k1.view(T, Hkv, D), v.view(T, Hkv, D), pos, cache, neox, mk, mv, slots, ks, vs)
+    q2, k2 = q.clone(), k.clone()
+    cops.rotary_embedding(pos, q2, k2, D, cache, neox)
+    if fp8:
+        cops.reshape_and_cache_flash(k2.view(T, Hkv, D), v.view(T, Hkv, D), rk.view(torch.float8_e4m3fn), rv.view(torch.float8_e4m3fn),
+                                     slots, "fp8", ks, vs)
+    else:
+        cops.reshape_and_cache_flash(k2.view(T, Hkv, D), v.view(T, Hkv, D), rk, rv, slots, "auto", ks, vs)
+    torch.cuda.synchronize()
+    assert torch.equal(q1.view(torch.int16), q2.view(torch.int16)), int((q1.view(torch.int16) != q2.view(torch.int16)).sum())
+    assert torch.equal(k1.view(torch.int16), k2.view(torch.int16))
+    if fp8:
+        assert torch.equal(mine, ref), int((mine != ref).sum())
+    else:
+        assert torch.equal(mine.view(torch.int16), ref.view(torch.int16))

@@ -39,8 +39,8 @@ def test_oracle_rotation_bit_exact_vs_vllm_native(golden, name):
     cache = _dec(g[name + "_cache"], act)
     q = _dec(g[name + "_q"], act).reshape(T, Hq, D)
     k = _dec(g[name + "_k"], act).reshape(T, Hkv, D)
-    q2 = O.rope_ref(q, g[name + "_pos"], cache, rot, bool(neox), act)
-    k2 = O.rope_ref(k, g[name + "_pos"], cache, rot, bool(neox), act)
+    q2 = O.rope_ref(q, g[name + "_pos"], cache, rot, bool(neox), act, each_op=True)
+    k2 = O.rope_ref(k, g[name + "_pos"], cache, rot, bool(neox), act, each_op=True)
     assert np.array_equal(_enc(q2, act).reshape(T, -1), g[name + "_q_out"])
     assert np.array_equal(_enc(k2, act).reshape(T, -1), g[name + "_k_out"])
 
@@ -84,7 +84,7 @@ def test_kernel_rotation_bit_exact_vs_vllm_golden(golden, name):
     kc, vc = phys.permute(0, 1, 3, 2, 4).unbind(1)
     slots = torch.arange(T, dtype=torch.int64, device="cuda")
     one = torch.ones(1, dtype=torch.float32, device="cuda")
-    torch.ops.b200attn.rope_kv_write(q, k, v, pos, cache, bool(neox), kc, vc, slots, one, one)
+    torch.ops.b200attn.rope_kv_write(q, k, v, pos, cache, bool(neox), kc, vc, slots, one, one, True)   # torch-native rounding
     torch.cuda.synchronize()
     assert np.array_equal(_bits(q).reshape(T, -1), g[name + "_q_out"])
     assert np.array_equal(_bits(k).reshape(T, -1), g[name + "_k_out"])
@@ -94,10 +94,11 @@ def test_kernel_rotation_bit_exact_vs_vllm_golden(golden, name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("each_op", [False, True])
 @pytest.mark.parametrize("act,kv,neox,rot,per_head", [
     ("bf16", "fp8", True, 128, False), ("bf16", "fp8", False, 128, True), ("fp16", "fp8", True, 64, True),
     ("bf16", "bf16", True, 128, False), ("fp16", "fp16", False, 32, False)])
-def test_rope_kv_write_matches_oracle_bitwise(act, kv, neox, rot, per_head):
+def test_rope_kv_write_matches_oracle_bitwise(act, kv, neox, rot, per_head, each_op):
     import ht_vllm_omni_b200.ops  # noqa: F401
     rng = np.random.default_rng(5)
     T, Hq, Hkv, D, bs, nb, max_pos = 37, 16, 2, 128, 16, 8, 5000
@@ -122,9 +123,9 @@ def test_rope_kv_write_matches_oracle_bitwise(act, kv, neox, rot, per_head):
     kc_ref = np.zeros((nb, bs, Hkv, D), np.uint8 if fp8 else np.float32)
     vc_ref = np.zeros_like(kc_ref)
     q_ref, k_ref = O.rope_kv_write_ref(qn, kn, vn, pos_np, cache_np, rot, neox, act, kc_ref, vc_ref, slots_np,
-                                       ks if fp8 else None, vs if fp8 else None, fp8)
+                                       ks if fp8 else None, vs if fp8 else None, fp8, each_op)
     torch.ops.b200attn.rope_kv_write(q, k, v, torch.from_numpy(pos_np).cuda(), cache, neox, kc, vc,
-                                     torch.from_numpy(slots_np).cuda(), torch.from_numpy(ks).cuda(), torch.from_numpy(vs).cuda())
+                                     torch.from_numpy(slots_np).cuda(), torch.from_numpy(ks).cuda(), torch.from_numpy(vs).cuda(), each_op)
     torch.cuda.synchronize()
     assert np.array_equal(q.float().cpu().numpy(), q_ref)
     assert np.array_equal(k.float().cpu().numpy(), k_ref)
