@@ -91,16 +91,17 @@ __device__ __forceinline__ uint2 quant8(const float (&f)[8], float scale) {
 template <int DT, bool FP8>
 __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p) {
   using E = Elem<DT>;
-  const int lanes = p.D >> 4;
-  const int units = p.Hq + 2 * p.Hkv;
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t row = gid / lanes;
+  // 32-bit index math (the host rejects launches with >= 2^31 threads): 64-bit divisions would cost more than the rotation
+  const uint32_t lanes = (uint32_t)p.D >> 4;
+  const uint32_t units = (uint32_t)(p.Hq + 2 * p.Hkv);
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t row = gid / lanes;
   const int j = (int)(gid - row * lanes);
   pdl_launch_dependents();
   pdl_wait();
-  if (row >= (int64_t)p.T * units) return;
+  if (row >= (uint32_t)p.T * units) return;
   const int t = (int)(row / units);
-  const int u = (int)(row - (int64_t)t * units);
+  const int u = (int)(row - (uint32_t)t * units);
   const int kind = u < p.Hq ? 0 : (u < p.Hq + p.Hkv ? 1 : 2);   // q, k, v
   const int h = kind == 0 ? u : (kind == 1 ? u - p.Hq : u - p.Hq - p.Hkv);
   const int64_t slot = p.slot_mapping[t];
@@ -236,6 +237,10 @@ extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q
   const int64_t threads = (int64_t)num_tokens * (num_q_heads + 2 * num_kv_heads) * (head_dim / 16);
   const int block = 256;
   const int64_t grid = (threads + block - 1) / block;
+  if (threads >= (1ll << 31)) {
+    set_error("rope_kv_write: %lld work items exceed the 2^31 limit of one launch; split the token range", (long long)threads);
+    return B200ATTN_EINVAL;
+  }
   const void* fn;
   if (fp8)
     fn = in_dtype == B200ATTN_BF16 ? (const void*)rope_kv_write_kernel<B200ATTN_BF16, true> : (const void*)rope_kv_write_kernel<B200ATTN_FP16, true>;
