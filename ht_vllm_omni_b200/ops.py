@@ -251,6 +251,21 @@ def _(parts_o, parts_lse, out, lse_out) -> None:
     return None
 
 
+def aligned_grid(max_ctas: int, num_seqs: int, num_q_heads: int, num_kv_heads: int) -> int:
+    """Decode grid for a batch (host-side shape arithmetic, capture-safe).  When the (sequence, kv head) pairs are few
+    enough that each can get k >= 2 CTAs, the grid is rounded down to pairs * k (if that keeps >= 80 % of the resident
+    CTAs): with equal-length sequences every CTA then owns exactly 1/k of ONE pair -- a single segment, a k-way merge and
+    no mid-range segment switch (c2: 296 -> 256 CTAs, +2.5 %; 32 x 4k: +14 %).  Ragged batches are still cut into equal
+    tile counts by the plan kernel, whatever the grid."""
+    group = max(1, num_q_heads // max(1, num_kv_heads))
+    pairs = num_seqs * num_kv_heads * (-(-group // 16))
+    if pairs > 0:
+        k = max_ctas // pairs
+        if k >= 2 and pairs * k * 10 >= max_ctas * 8:
+            return pairs * k
+    return max_ctas
+
+
 # ------------------------------------------------------------------------------------------------
 # Convenience wrapper owning the plan / workspace buffers (what the metadata builder keeps per device)
 # ------------------------------------------------------------------------------------------------
@@ -275,20 +290,10 @@ class DecodeWorkspace:
         self._no_map = torch.empty(0, dtype=torch.int32, device=self.device)
 
     def grid_for(self, num_seqs: int, num_q_heads: int, num_kv_heads: int) -> int:
-        """Decode grid for a batch (host-side shape arithmetic, capture-safe).  When the (sequence, kv head) pairs are few
-        enough that each can get k >= 2 CTAs, the grid is rounded down to pairs * k (if that keeps >= 80 % of the resident
-        CTAs): with equal-length sequences every CTA then owns exactly 1/k of ONE pair -- a single segment, a k-way merge
-        and no mid-range segment switch (c2: 296 -> 256 CTAs, +2.5 %; 32 x 4k: +14 %).  Ragged batches are still cut into
-        equal tile counts by the plan kernel, whatever the grid."""
+        """Decode grid of the next plan: `aligned_grid` unless the workspace was built with an explicit grid."""
         if self._fixed_grid:
             return self.num_ctas
-        group = max(1, num_q_heads // max(1, num_kv_heads))
-        pairs = num_seqs * num_kv_heads * (-(-group // 16))
-        if pairs > 0:
-            k = self.num_ctas // pairs
-            if k >= 2 and pairs * k * 10 >= self.num_ctas * 8:
-                return pairs * k
-        return self.num_ctas
+        return aligned_grid(self.num_ctas, num_seqs, num_q_heads, num_kv_heads)
 
     def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int) -> None:
         if seq_lens.shape[0] > self.max_num_seqs:

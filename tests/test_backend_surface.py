@@ -120,3 +120,19 @@ def test_impl_profile_run_and_no_cpu_fallback():
         impl.do_kv_cache_update(layer, key, key, cache, torch.zeros(3, dtype=torch.int64))
     with pytest.raises(B.B200AttnError):
         impl._planes(torch.zeros(2, 4, 16, 2, 128, dtype=torch.uint8))
+
+
+def test_aligned_grid_policy():
+    """ops.aligned_grid: pair-aligned decode grids only when every pair gets >= 2 CTAs and >= 80 % of the slots stay used."""
+    from ht_vllm_omni_b200.ops import aligned_grid
+    assert aligned_grid(296, 64, 16, 2) == 256      # c2: 128 pairs x 2
+    assert aligned_grid(296, 32, 32, 4) == 256      # thinker B=32: 128 pairs x 2
+    assert aligned_grid(296, 32, 16, 2) == 256      # 64 pairs x 4
+    assert aligned_grid(296, 1, 16, 2) == 296       # 2 pairs x 148
+    assert aligned_grid(296, 100, 16, 2) == 296     # 200 pairs: k = 1 -> default
+    assert aligned_grid(296, 256, 16, 2) == 296     # more pairs than CTAs
+    assert aligned_grid(296, 50, 16, 2) == 296      # 100 pairs x 2 = 200 < 80 % of 296 -> default
+    assert aligned_grid(296, 0, 16, 2) == 296
+    for b in range(1, 300):
+        g = aligned_grid(296, b, 16, 2)
+        assert 0.8 * 296 <= g <= 296
