@@ -201,6 +201,21 @@ B200ATTN_API int b200attn_merge_lse(const void* parts_o, const float* parts_lse,
                        int32_t head_dim, int32_t dtype, void* stream);
 
 /*
+ * KV hand-off gather (the step after the path).
+ * Replaces: the per-layer index -> flatten -> truncate loop of OmniKVTransferManager._extract_kv_cache
+ *   (vllm_omni/distributed/omni_connectors/kv_transfer_manager.py:224-301; layouts utils/kv_utils.py:13-85).
+ * For every layer l and plane in {K, V}:  out[l][plane][i][h][:] = plane_l[block_ids[i / block_size]][i % block_size][h][:]
+ * for i < n_tokens (the caller passes n_tokens = min(seq_len, n_ids * block_size) and only in-range ids, as the reference
+ * filters them; an out-of-range id is zero-filled, never dereferenced).  Raw bytes: row_bytes = head_dim * element size.
+ * k_planes / v_planes are DEVICE arrays of num_layers plane base pointers; all layers share the three BYTE strides.
+ * `out` holds num_layers * 2 * n_tokens * num_kv_heads * row_bytes bytes; one pinned D2H of it replaces 2 x num_layers copies.
+ */
+B200ATTN_API int b200attn_kv_gather(const void* const* k_planes, const void* const* v_planes, int32_t num_layers,
+                       int64_t stride_block_bytes, int64_t stride_slot_bytes, int64_t stride_head_bytes,
+                       int64_t num_blocks, const int32_t* block_ids, int32_t n_tokens, int32_t num_kv_heads,
+                       int32_t block_size, int32_t row_bytes, void* out, void* stream);
+
+/*
  * Runtime knobs (host, process-wide): "pdl" (programmatic dependent launch, default 1),
  * "force_simt" (route every group size to the CUDA-core consumer, default 0).
  * Returns the previous value or B200ATTN_EINVAL for an unknown name.

@@ -180,6 +180,28 @@ def rope_kv_write_ref(query, key, value, positions, cos_sin_cache, rotary_dim, i
 
 
 # ------------------------------------------------------------------------------------------------
+# KV hand-off gather  
+# ------------------------------------------------------------------------------------------------
+
+
+def kv_extract_ref(block_ids, seq_len, key_blocks, value_blocks):
+    """One layer of OmniKVTransferManager._extract_kv_cache
+    ($REF/vllm_omni/distributed/omni_connectors/kv_transfer_manager.py:266-282): key_blocks / value_blocks are
+    [num_blocks, block_size, n_heads, head_dim] arrays of any dtype (raw fp8 bytes included).  Ids outside [0, num_blocks)
+    are dropped (:269-270), the selected blocks are flattened over (block, slot) (:276-279) and cut to seq_len (:280-282).
+    Returns (flat_k, flat_v) or None when no id is valid (:271-272)."""
+    max_block = min(key_blocks.shape[0], value_blocks.shape[0]) - 1
+    valid = [b for b in block_ids if 0 <= b <= max_block]
+    if not valid:
+        return None
+    fk = key_blocks[valid].reshape((-1,) + key_blocks.shape[2:])
+    fv = value_blocks[valid].reshape((-1,) + value_blocks.shape[2:])
+    if seq_len < fk.shape[0]:
+        fk, fv = fk[:seq_len], fv[:seq_len]
+    return np.ascontiguousarray(fk), np.ascontiguousarray(fv)
+
+
+# ------------------------------------------------------------------------------------------------
 # paged decode attention (q_len = 1)
 # ------------------------------------------------------------------------------------------------
 
