@@ -59,7 +59,8 @@ def gather_request_kv(block_ids: Sequence[int], seq_len: int, kv_caches: Sequenc
     key_cache: list = [None] * num_layers
     value_cache: list = [None] * num_layers
     L = len(live)
-    host = torch.empty((L, 2, n_tokens, H, D), dtype=k0.dtype).pin_memory()
+    # straight from torch's caching pinned-host allocator (no pageable detour; blocks of finished requests are reused)
+    host = torch.empty((L, 2, n_tokens, H, D), dtype=k0.dtype, pin_memory=True)
     if n_tokens > 0:
         with torch.cuda.device(dev):
             ids = torch.tensor(valid, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
