@@ -28,25 +28,26 @@ struct KvGatherParams {
 __global__ void __launch_bounds__(256) kv_gather_kernel(const KvGatherParams p) {
   pdl_wait();
   pdl_launch_dependents();
+  // blockIdx.y = layer * 2 + plane; blockIdx.x covers the plane's n_tokens * Hkv * (row_bytes / 16) vectors in 32-bit math
+  // (the first version did three 64-bit divisions per 16 bytes and was issue-bound at 75 %: profiles/r01_ncu_kv_gather_v8.txt)
   const uint32_t vec_per_row = (uint32_t)p.row_bytes >> 4;
-  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t rows = (uint64_t)p.num_layers * 2 * p.n_tokens * p.Hkv;
-  const uint64_t row = gid / vec_per_row;
-  if (row >= rows) return;
-  const uint32_t c = (uint32_t)(gid - row * vec_per_row);
-  const uint32_t h = (uint32_t)(row % p.Hkv);
-  const uint64_t r1 = row / p.Hkv;
-  const uint32_t tok = (uint32_t)(r1 % p.n_tokens);
-  const uint64_t r2 = r1 / p.n_tokens;
-  const uint32_t kv = (uint32_t)(r2 & 1);
-  const uint32_t layer = (uint32_t)(r2 >> 1);
-  const int32_t blk = __ldg(p.block_ids + tok / p.block_size);
-  const uint32_t slot = tok % p.block_size;
+  const uint32_t per_plane = (uint32_t)p.n_tokens * p.Hkv * vec_per_row;
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= per_plane) return;
+  const uint32_t rowi = idx / vec_per_row;
+  const uint32_t c = idx - rowi * vec_per_row;
+  const uint32_t tok = rowi / p.Hkv;
+  const uint32_t h = rowi - tok * p.Hkv;
+  const uint32_t kv = blockIdx.y & 1, layer = blockIdx.y >> 1;
+  const uint32_t bi = tok / p.block_size;
+  const int32_t blk = __ldg(p.block_ids + bi);
+  const uint32_t slot = tok - bi * p.block_size;
   uint4 v = make_uint4(0u, 0u, 0u, 0u);
   if (blk >= 0 && blk < p.num_blocks) {
     const uint8_t* base = reinterpret_cast<const uint8_t*>(kv ? p.v_planes[layer] : p.k_planes[layer]);
     v = __ldg(reinterpret_cast<const uint4*>(base + blk * p.stride_block + slot * p.stride_slot + h * p.stride_head) + c);
   }
+  const uint64_t gid = (uint64_t)blockIdx.y * per_plane + idx;
   reinterpret_cast<uint4*>(p.out)[gid] = v;
 }
 
@@ -79,12 +80,12 @@ extern "C" int b200attn_kv_gather(const void* const* k_planes, const void* const
   p.stride_block = stride_block_bytes; p.stride_slot = stride_slot_bytes; p.stride_head = stride_head_bytes;
   p.num_blocks = num_blocks; p.block_ids = block_ids; p.out = reinterpret_cast<uint8_t*>(out);
   p.num_layers = num_layers; p.n_tokens = n_tokens; p.Hkv = num_kv_heads; p.block_size = block_size; p.row_bytes = row_bytes;
-  const int64_t threads = (int64_t)num_layers * 2 * n_tokens * num_kv_heads * (row_bytes / 16);
-  const int64_t grid = (threads + 255) / 256;
-  if (grid >= (1ll << 31)) {
-    set_error("kv_gather: %lld blocks exceed one launch; split the layer range", (long long)grid);
+  const int64_t per_plane = (int64_t)n_tokens * num_kv_heads * (row_bytes / 16);
+  const int64_t gx = (per_plane + 255) / 256;
+  if (per_plane >= (1ll << 32) || gx >= (1ll << 31) || 2ll * num_layers > 65535) {
+    set_error("kv_gather: %lld vectors per plane / %d layers exceed one launch; split the request", (long long)per_plane, num_layers);
     return B200ATTN_EINVAL;
   }
   void* args[] = {&p};
-  return launch_with_pdl((const void*)kv_gather_kernel, dim3((unsigned)grid), dim3(256), 0, static_cast<cudaStream_t>(stream), args);
+  return launch_with_pdl((const void*)kv_gather_kernel, dim3((unsigned)gx, (unsigned)(2 * num_layers)), dim3(256), 0, static_cast<cudaStream_t>(stream), args);
 }
