@@ -60,22 +60,23 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
   const int h = (int)(row % p.Hkv);
   const int kv = (int)((row / p.Hkv) & 1);
   const int t = (int)(row / (2 * p.Hkv));
-  const int64_t slot = p.slot_mapping[t];
-  if (slot < 0) return;  // padding token
-  const int64_t blk = slot / p.block_size;
-  const int64_t off = slot - blk * p.block_size;
-
+  // the slot, the two data vectors and the scale are independent loads: issue them together (one memory round trip on the
+  // critical path between two decode kernels instead of two); a padding token's key/value row exists, reading it is harmless
   using E = Elem<IN_DT>;
   const typename E::type* src =
       kv ? reinterpret_cast<const typename E::type*>(p.value) + (int64_t)t * p.value_stride_t + (int64_t)h * p.value_stride_h
          : reinterpret_cast<const typename E::type*>(p.key) + (int64_t)t * p.key_stride_t + (int64_t)h * p.key_stride_h;
+  const int64_t slot = __ldg(p.slot_mapping + t);
   const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(src + col));
   const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(src + col + 8));
+  float scale = 1.0f;
+  if constexpr (FP8) scale = __ldg((kv ? p.v_scale : p.k_scale) + (int64_t)h * p.scale_stride);
+  if (slot < 0) return;  // padding token
+  const int64_t blk = slot / p.block_size;
+  const int64_t off = slot - blk * p.block_size;
   const int64_t dst_off = blk * p.stride_block + off * p.stride_slot + (int64_t)h * p.stride_head + col;
 
   if constexpr (FP8) {
-    const float* sp = kv ? p.v_scale : p.k_scale;
-    const float scale = __ldg(sp + (int64_t)h * p.scale_stride);
     float f[16];
     unpack8<IN_DT>(r0, *reinterpret_cast<float(*)[8]>(&f[0]));
     unpack8<IN_DT>(r1, *reinterpret_cast<float(*)[8]>(&f[8]));

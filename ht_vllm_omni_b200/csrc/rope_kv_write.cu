@@ -104,8 +104,9 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
   const int u = (int)(row - (uint32_t)t * units);
   const int kind = u < p.Hq ? 0 : (u < p.Hq + p.Hkv ? 1 : 2);   // q, k, v
   const int h = kind == 0 ? u : (kind == 1 ? u - p.Hq : u - p.Hq - p.Hkv);
-  const int64_t slot = p.slot_mapping[t];
-  if (kind == 2 && slot < 0) return;
+  // slot, position and the data vectors are independent loads, issued together (see kv_write.cu)
+  const int64_t slot = __ldg(p.slot_mapping + t);
+  const int64_t pos = __ldg(p.positions + t);
 
   const int half = p.rot >> 1;
   const bool rotary = kind != 2 && j < (p.rot >> 4);
@@ -122,9 +123,9 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
   float c0[8], c1[8];
   load8<DT>(base, roff + a0, c0);
   load8<DT>(base, roff + a1, c1);
+  if (kind == 2 && slot < 0) return;   // padding token: nothing to write
 
   if (rotary) {
-    const int64_t pos = p.positions[t];
     float cs[8], sn[8];
     load8<DT>(p.cos_sin, pos * p.rot + 8 * j, cs);
     load8<DT>(p.cos_sin, pos * p.rot + half + 8 * j, sn);
