@@ -49,6 +49,7 @@ PROTOTYPES = {
                                   _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32, _p, _sz, _p, _p, _i32, _i32, _p]),
     "b200attn_merge": (C.c_int, [_p, _i32, _p, _p, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p]),
     "b200attn_merge_lse": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
+    "b200attn_merge_lse_peers": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
     "b200attn_set_option": (C.c_int, [C.c_char_p, _i32]),
 }
 

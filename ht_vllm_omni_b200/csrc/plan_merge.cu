@@ -209,6 +209,40 @@ __global__ void __launch_bounds__(128) merge_lse_kernel(const void* parts_o, con
   if (lane == 0 && lse_out) lse_out[row] = den > 0.f ? mx + __logf(den) : -INFINITY;
 }
 
+// Same combine with the P parts living in P different buffers -- the ranks' symmetric-memory buffers of a sequence-split
+// group, read straight over NVLink (peer loads bypass the caches: the buffers are rewritten every other layer).  One warp
+// per (row, head); lanes stride the head dim.
+template <int DT>
+__global__ void __launch_bounds__(128) merge_lse_peers_kernel(const void* const* o_ptrs, const float* const* lse_ptrs, int P,
+                                                              int64_t o_off, int64_t lse_off, void* out, float* lse_out,
+                                                              int64_t rows, int D) {
+  pdl_wait();
+  pdl_launch_dependents();
+  using E = Elem<DT>;
+  const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float mx = -INFINITY;
+  for (int i = 0; i < P; ++i) mx = fmaxf(mx, __ldcv(lse_ptrs[i] + lse_off + row));
+  float den = 0.f;
+  for (int i = 0; i < P; ++i) {
+    const float l = __ldcv(lse_ptrs[i] + lse_off + row);
+    den += (l == -INFINITY) ? 0.f : __expf(l - mx);
+  }
+  typename E::type* oo = reinterpret_cast<typename E::type*>(out);
+  for (int d = lane; d < D; d += 32) {
+    float acc = 0.f;
+    for (int i = 0; i < P; ++i) {
+      const float l = __ldcv(lse_ptrs[i] + lse_off + row);
+      const float wgt = (l == -INFINITY) ? 0.f : __expf(l - mx);
+      const unsigned short raw = __ldcv(reinterpret_cast<const unsigned short*>(o_ptrs[i]) + o_off + row * D + d);
+      acc += wgt * E::to_float(*reinterpret_cast<const typename E::type*>(&raw));
+    }
+    oo[row * D + d] = E::from_float(den > 0.f ? acc / den : 0.f);
+  }
+  if (lane == 0 && lse_out) lse_out[row] = den > 0.f ? mx + __logf(den) : -INFINITY;
+}
+
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
 
 static int split_group(int Hq, int Hkv, int* G, int* gsplit) {
@@ -321,5 +355,24 @@ extern "C" int b200attn_merge_lse(const void* parts_o, const float* parts_lse, i
   int P = num_parts, D = head_dim;
   const void* fn = dtype == B200ATTN_BF16 ? (const void*)merge_lse_kernel<B200ATTN_BF16> : (const void*)merge_lse_kernel<B200ATTN_FP16>;
   void* args[] = {(void*)&parts_o, (void*)&parts_lse, &P, &part_stride_o, &part_stride_lse, &out, &lse_out, &rows, &D};
+  return launch_with_pdl(fn, dim3((unsigned)((rows + 3) / 4)), dim3(128), 0, static_cast<cudaStream_t>(stream), args);
+}
+
+extern "C" int b200attn_merge_lse_peers(const void* const* parts_o_ptrs, const float* const* parts_lse_ptrs, int32_t num_parts,
+                                        int64_t o_offset, int64_t lse_offset, void* out, float* lse_out, int32_t n,
+                                        int32_t num_q_heads, int32_t head_dim, int32_t dtype, void* stream) {
+  if (n == 0) return B200ATTN_OK;
+  if (!parts_o_ptrs || !parts_lse_ptrs || !out || num_parts <= 0) {
+    set_error("merge_lse_peers: null pointer or no parts");
+    return B200ATTN_EINVAL;
+  }
+  if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) {
+    set_error("merge_lse_peers: dtype must be bf16 or fp16");
+    return B200ATTN_EINVAL;
+  }
+  int64_t rows = (int64_t)n * num_q_heads;
+  int P = num_parts, D = head_dim;
+  const void* fn = dtype == B200ATTN_BF16 ? (const void*)merge_lse_peers_kernel<B200ATTN_BF16> : (const void*)merge_lse_peers_kernel<B200ATTN_FP16>;
+  void* args[] = {(void*)&parts_o_ptrs, (void*)&parts_lse_ptrs, &P, &o_offset, &lse_offset, &out, &lse_out, &rows, &D};
   return launch_with_pdl(fn, dim3((unsigned)((rows + 3) / 4)), dim3(128), 0, static_cast<cudaStream_t>(stream), args);
 }

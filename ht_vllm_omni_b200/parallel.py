@@ -138,3 +138,48 @@ def dcp_combine(out_part: torch.Tensor, lse_part: torch.Tensor, group=None, merg
         return out
     hl = Hg // world
     return out[:, rank * hl:(rank + 1) * hl]
+
+
+class PeerExchange:
+    """Sequence-split combine over NVLink peer memory instead of NCCL (SURVEY.md §8e remedy 1, "write partials peer-to-peer
+    into a symmetric buffer and run Kernel 3"): every rank of the group decodes straight into its slot of a torch
+    symmetric-memory buffer, one device-side barrier orders the writes, and `b200attn_merge_lse_peers` reads all ranks'
+    partials with peer loads while it merges.  Two slots alternate, so a rank that runs ahead cannot overwrite a partial a
+    peer is still reading (it would have to pass the NEXT barrier first, which that peer only joins after its merge).
+    One launch + one barrier per layer replace two all-gathers, three allocations and a merge launch.
+    """
+
+    def __init__(self, max_rows: int, group_heads: int, head_dim: int, dtype: torch.dtype, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.T, self.Hg, self.D, self.dtype = max_rows, group_heads, head_dim, dtype
+        self.o = symm_mem.empty((2, max_rows, group_heads, head_dim), dtype=dtype, device=device)
+        self.lse = symm_mem.empty((2, max_rows, group_heads), dtype=torch.float32, device=device)
+        self.h_o = symm_mem.rendezvous(self.o, self.group)
+        self.h_lse = symm_mem.rendezvous(self.lse, self.group)
+        self.slot = 0
+
+    def buffers(self) -> tuple[torch.Tensor, torch.Tensor]:
+        """(out, lse) views of the NEXT slot: pass them to the local decode call so it writes the partial in place."""
+        self.slot ^= 1
+        return self.o[self.slot], self.lse[self.slot]
+
+    def combine(self, num_rows: int, keep_local_heads: bool = True) -> torch.Tensor:
+        """Barrier + peer-memory merge of the slot handed out by the last `buffers()` call."""
+        from ._lib import DT_BF16, DT_FP16, check, load_library
+
+        dev = self.o.device
+        self.h_o.barrier(channel=self.slot)
+        out = torch.empty((num_rows, self.Hg, self.D), dtype=self.dtype, device=dev)
+        stream = torch.cuda.current_stream(dev)
+        check(load_library().b200attn_merge_lse_peers(
+            self.h_o.buffer_ptrs_dev, self.h_lse.buffer_ptrs_dev, self.world,
+            self.slot * self.T * self.Hg * self.D, self.slot * self.T * self.Hg, out.data_ptr(), None, num_rows, self.Hg, self.D,
+            DT_BF16 if self.dtype == torch.bfloat16 else DT_FP16, stream.cuda_stream), "b200attn_merge_lse_peers")
+        if not keep_local_heads:
+            return out
+        hl = self.Hg // self.world
+        return out[:, self.rank * hl:(self.rank + 1) * hl]

@@ -201,6 +201,19 @@ B200ATTN_API int b200attn_merge_lse(const void* parts_o, const float* parts_lse,
                        int32_t head_dim, int32_t dtype, void* stream);
 
 /*
+ * The same combine over PEER memory (NVLink / NVSwitch): part p is read from parts_o_ptrs[p] + o_offset (elements of
+ * dtype, laid out [n][Hq][D]) and parts_lse_ptrs[p] + lse_offset (fp32 [n][Hq]) -- DEVICE arrays of num_parts pointers,
+ * e.g. torch symmetric-memory `buffer_ptrs_dev`, so the ranks of a sequence-split group exchange their partials with
+ * plain peer loads inside the merge kernel instead of two NCCL all-gathers.  The caller orders the peers' writes before
+ * this launch (a symmetric-memory barrier) and alternates two offsets so a buffer is not rewritten while a peer reads it.
+ * Replaces: cp_lse_ag_out_rs ($VLLM/v1/attention/backends/flashinfer.py:1714-1738).
+ */
+B200ATTN_API int b200attn_merge_lse_peers(const void* const* parts_o_ptrs, const float* const* parts_lse_ptrs,
+                             int32_t num_parts, int64_t o_offset, int64_t lse_offset,
+                             void* out, float* lse_out, int32_t n, int32_t num_q_heads,
+                             int32_t head_dim, int32_t dtype, void* stream);
+
+/*
  * KV hand-off gather (the step after the path).
  * Replaces: the per-layer index -> flatten -> truncate loop of OmniKVTransferManager._extract_kv_cache
  *   (vllm_omni/distributed/omni_connectors/kv_transfer_manager.py:224-301; layouts utils/kv_utils.py:13-85).

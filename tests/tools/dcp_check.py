@@ -79,6 +79,40 @@ if rank == 0:
     print(f"dcp{world} over NCCL: max |sequence-split - unsharded| = {t.item():.5f} (tolerance 1e-2); "
           f"combine (2 all-gathers + merge_lse) {evs[0].elapsed_time(evs[1]) / 20 * 1e3:.1f} us per layer", flush=True)
 assert t.item() <= 1e-2, t.item()
+
+# ---- the same exchange over NVLink peer memory: decode writes its partial into a symmetric buffer, barrier, peer-load merge ----
+px = P.PeerExchange(B, Hg, D, torch.bfloat16, dev)
+ws = ops.DecodeWorkspace(dev, B, torch.uint8, group_size=Hg)
+ws.make_plan(ln, Hg, 1)
+
+
+def layer():
+    o_buf, lse_buf = px.buffers()
+    lse_buf.fill_(float("-inf"))          # rows without tokens on this rank stay "empty part"
+    ws.decode(q_group, kc, vc, bt, ln, o_buf, ks, vs, D ** -0.5, lse=lse_buf)
+    return px.combine(B)
+
+
+got2 = layer()
+for _ in range(3):
+    got2 = layer()
+torch.cuda.synchronize(); dist.barrier()
+e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+e0.record()
+for _ in range(20):
+    got2 = layer()
+e1.record()
+for _ in range(20):
+    o_buf, lse_buf = px.buffers(); lse_buf.fill_(float("-inf"))
+    ws.decode(q_group, kc, vc, bt, ln, o_buf, ks, vs, D ** -0.5, lse=lse_buf)
+e2.record(); torch.cuda.synchronize()
+err2 = (got2.float() - full_out[:, rank * Hl:(rank + 1) * Hl].float()).abs().max().item()
+t2 = torch.tensor([err2], device=dev); dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+if rank == 0:
+    comb = (e0.elapsed_time(e1) - e1.elapsed_time(e2)) / 20 * 1e3
+    print(f"dcp{world} over NVLink peer memory: max |sequence-split - unsharded| = {t2.item():.5f}; decode+combine "
+          f"{e0.elapsed_time(e1) / 20 * 1e3:.1f} us per layer, of which barrier + peer-load merge {comb:.1f} us", flush=True)
+assert t2.item() <= 1e-2, t2.item()
 dist.barrier(); torch.cuda.synchronize()
 sys.stdout.flush()
 os._exit(0)
