@@ -212,6 +212,15 @@ __global__ void __launch_bounds__(128) merge_lse_kernel(const void* parts_o, con
 // Same combine with the P parts living in P different buffers -- the ranks' symmetric-memory buffers of a sequence-split
 // group, read straight over NVLink (peer loads bypass the caches: the buffers are rewritten every other layer).  One warp
 // per (row, head); lanes stride the head dim.
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+// Half a warp per (row, head): 16 lanes x 8 head dims (one 16-byte peer load per part and lane); all of a row's loads are
+// issued before anything is consumed, so the merge costs two NVLink round trips (lse, then o) whatever P is.  D must be 128.
+constexpr int kMaxPeerParts = 8;
 template <int DT>
 __global__ void __launch_bounds__(128) merge_lse_peers_kernel(const void* const* o_ptrs, const float* const* lse_ptrs, int P,
                                                               int64_t o_off, int64_t lse_off, void* out, float* lse_out,
@@ -219,28 +228,41 @@ __global__ void __launch_bounds__(128) merge_lse_peers_kernel(const void* const*
   pdl_wait();
   pdl_launch_dependents();
   using E = Elem<DT>;
-  const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 4);
   if (row >= rows) return;
-  const int lane = threadIdx.x & 31;
-  float mx = -INFINITY;
-  for (int i = 0; i < P; ++i) mx = fmaxf(mx, __ldcv(lse_ptrs[i] + lse_off + row));
-  float den = 0.f;
-  for (int i = 0; i < P; ++i) {
-    const float l = __ldcv(lse_ptrs[i] + lse_off + row);
-    den += (l == -INFINITY) ? 0.f : __expf(l - mx);
-  }
-  typename E::type* oo = reinterpret_cast<typename E::type*>(out);
-  for (int d = lane; d < D; d += 32) {
-    float acc = 0.f;
-    for (int i = 0; i < P; ++i) {
-      const float l = __ldcv(lse_ptrs[i] + lse_off + row);
-      const float wgt = (l == -INFINITY) ? 0.f : __expf(l - mx);
-      const unsigned short raw = __ldcv(reinterpret_cast<const unsigned short*>(o_ptrs[i]) + o_off + row * D + d);
-      acc += wgt * E::to_float(*reinterpret_cast<const typename E::type*>(&raw));
+  const int l16 = threadIdx.x & 15;
+  float lse[kMaxPeerParts];
+  uint4 ov[kMaxPeerParts];
+#pragma unroll
+  for (int i = 0; i < kMaxPeerParts; ++i) {
+    if (i < P) {
+      lse[i] = __ldcv(lse_ptrs[i] + lse_off + row);
+      ov[i] = ld_peer_v4(reinterpret_cast<const typename E::type*>(o_ptrs[i]) + o_off + row * D + l16 * 8);
     }
-    oo[row * D + d] = E::from_float(den > 0.f ? acc / den : 0.f);
   }
-  if (lane == 0 && lse_out) lse_out[row] = den > 0.f ? mx + __logf(den) : -INFINITY;
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < kMaxPeerParts; ++i)
+    if (i < P) mx = fmaxf(mx, lse[i]);
+  float den = 0.f, acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxPeerParts; ++i) {
+    if (i < P) {
+      const float wgt = (lse[i] == -INFINITY) ? 0.f : __expf(lse[i] - mx);
+      den += wgt;
+      const typename E::type* e = reinterpret_cast<const typename E::type*>(&ov[i]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += wgt * E::to_float(e[k]);
+    }
+  }
+  uint4 res;
+  typename E::type* r = reinterpret_cast<typename E::type*>(&res);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) r[k] = E::from_float(den > 0.f ? acc[k] / den : 0.f);
+  *reinterpret_cast<uint4*>(reinterpret_cast<typename E::type*>(out) + row * D + l16 * 8) = res;
+  if (l16 == 0 && lse_out) lse_out[row] = den > 0.f ? mx + __logf(den) : -INFINITY;
 }
 
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
@@ -370,9 +392,13 @@ extern "C" int b200attn_merge_lse_peers(const void* const* parts_o_ptrs, const f
     set_error("merge_lse_peers: dtype must be bf16 or fp16");
     return B200ATTN_EINVAL;
   }
+  if (head_dim != 128 || num_parts > kMaxPeerParts) {
+    set_error("merge_lse_peers: head_dim must be 128 and num_parts <= %d", kMaxPeerParts);
+    return B200ATTN_EINVAL;
+  }
   int64_t rows = (int64_t)n * num_q_heads;
   int P = num_parts, D = head_dim;
   const void* fn = dtype == B200ATTN_BF16 ? (const void*)merge_lse_peers_kernel<B200ATTN_BF16> : (const void*)merge_lse_peers_kernel<B200ATTN_FP16>;
   void* args[] = {(void*)&parts_o_ptrs, (void*)&parts_lse_ptrs, &P, &o_offset, &lse_offset, &out, &lse_out, &rows, &D};
-  return launch_with_pdl(fn, dim3((unsigned)((rows + 3) / 4)), dim3(128), 0, static_cast<cudaStream_t>(stream), args);
+  return launch_with_pdl(fn, dim3((unsigned)((rows + 7) / 8)), dim3(128), 0, static_cast<cudaStream_t>(stream), args);
 }
