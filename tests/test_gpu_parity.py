@@ -324,6 +324,45 @@ def test_merge_lse_matches_oracle(ops):
     assert np.all(np.isneginf(lse.cpu().numpy()[~live])) and float(out[5, 3].abs().sum()) == 0
 
 
+def test_merge_lse_peers_matches_strided_merge_and_oracle(ops):
+    """b200attn_merge_lse_peers (the sequence-split combine over peer memory) on one GPU: the P "peer" buffers are P separate
+    local allocations reached through a device array of pointers, with a non-zero slot offset -- same result as the strided
+    merge_lse kernel and the oracle."""
+    import ctypes
+    from oracle import oracle as O
+    from ht_vllm_omni_b200._lib import DT_BF16, check, load_library
+
+    rng = np.random.default_rng(6)
+    P, n, Hq, D, slot = 3, 11, 8, 128, 1
+    po = rng.normal(size=(P, n, Hq, D)).astype(np.float32)
+    pl = rng.normal(size=(P, n, Hq)).astype(np.float32) * 3
+    pl[2, 4, :] = -np.inf
+    pl[:, 7, 1] = -np.inf
+    bufs_o = [torch.zeros(2, n, Hq, D, dtype=torch.bfloat16, device="cuda") for _ in range(P)]
+    bufs_l = [torch.zeros(2, n, Hq, dtype=torch.float32, device="cuda") for _ in range(P)]
+    for i in range(P):
+        bufs_o[i][slot].copy_(torch.from_numpy(po[i]).to(torch.bfloat16))
+        bufs_l[i][slot].copy_(torch.from_numpy(pl[i]))
+    o_ptrs = torch.tensor([b.data_ptr() for b in bufs_o], dtype=torch.int64, device="cuda")
+    l_ptrs = torch.tensor([b.data_ptr() for b in bufs_l], dtype=torch.int64, device="cuda")
+    out = torch.zeros(n, Hq, D, dtype=torch.bfloat16, device="cuda")
+    lse = torch.zeros(n, Hq, dtype=torch.float32, device="cuda")
+    check(load_library().b200attn_merge_lse_peers(o_ptrs.data_ptr(), l_ptrs.data_ptr(), P, slot * n * Hq * D, slot * n * Hq,
+                                                  out.data_ptr(), lse.data_ptr(), n, Hq, D, DT_BF16,
+                                                  torch.cuda.current_stream().cuda_stream), "b200attn_merge_lse_peers")
+    ref_out = torch.zeros_like(out)
+    ref_lse = torch.zeros_like(lse)
+    t_po = torch.stack([b[slot] for b in bufs_o])
+    torch.ops.b200attn.merge_lse(t_po, torch.stack([b[slot] for b in bufs_l]), ref_out, ref_lse)
+    torch.cuda.synchronize()
+    ro, rl = O.merge_lse_ref(t_po.float().cpu().numpy(), pl)
+    live = np.isfinite(rl)
+    assert_close(out.float().cpu().numpy()[live], ro[live], "bf16", "bf16")
+    assert torch.equal(out, ref_out)                      # same arithmetic as the strided kernel
+    assert np.allclose(lse.cpu().numpy()[live], rl[live], atol=1e-4)
+    assert np.all(np.isneginf(lse.cpu().numpy()[~live])) and float(out[7, 1].abs().sum()) == 0
+
+
 def test_cuda_graph_capture_and_replay(ops):
     """The whole step (plan + write + decode + merge) captures into a CUDA graph and replays on updated metadata
     (same buffers, new contents) -- the way vLLM's FULL cudagraph mode drives a backend."""
