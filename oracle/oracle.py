@@ -303,7 +303,8 @@ def merge_partials_ref(acc, M, Lsum):
 def merge_lse_ref(parts_o, parts_lse):
     """merge_attn_states generalised to P parts: parts_o [P, n, Hq, D], parts_lse [P, n, Hq] (natural log)."""
     mx = parts_lse.max(axis=0)
-    w = np.where(np.isneginf(parts_lse), 0.0, np.exp(parts_lse - mx[None])).astype(np.float32)
+    with np.errstate(invalid="ignore"):   # -inf - -inf for rows that are empty on every part
+        w = np.where(np.isneginf(parts_lse), 0.0, np.exp(parts_lse - mx[None])).astype(np.float32)
     den = w.sum(axis=0, dtype=np.float32)
     o = (parts_o * w[..., None]).sum(axis=0, dtype=np.float32) / np.where(den == 0, 1, den)[..., None]
     lse = np.where(den > 0, mx + np.log(np.where(den > 0, den, 1)), -np.inf).astype(np.float32)
