@@ -285,7 +285,7 @@ def run_ours(args, w):
     sm_scale = D ** -0.5
 
     def step():
-        ws.make_plan(d_lens, Hq, Hkv)
+        ws.make_plan(d_lens, Hq, Hkv, d_bt, bs)
         for l in range(NL):
             kc, vc = caches[l]
             torch.ops.b200attn.kv_write(kn[l], vn[l], kc, vc, step_slots, k_scale, v_scale)
@@ -372,7 +372,7 @@ def run_ours(args, w):
         for gi in range(NG):
             main.wait_event(ev_in[gi])
             if gi == 0:
-                ws.make_plan(d_lens, Hq, Hkv)
+                ws.make_plan(d_lens, Hq, Hkv, d_bt, bs)
             for l in range(gi * GL, (gi + 1) * GL):
                 kc, vc = caches[l]
                 torch.ops.b200attn.kv_write(kn[l], vn[l], kc, vc, step_slots, k_scale, v_scale)
@@ -429,7 +429,7 @@ def run_ours(args, w):
     # over the NL distinct layer caches captured as one CUDA graph with PDL off (no overlap between neighbours), CUDA events
     # around the replays on the launching stream; duration per launch = elapsed / launches ----
     lib.b200attn_set_option(b"pdl", 0)
-    ws.make_plan(d_lens, Hq, Hkv)
+    ws.make_plan(d_lens, Hq, Hkv, d_bt, bs)
     torch.cuda.synchronize()
 
     def decode_only():

@@ -185,21 +185,27 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
                                              group_size=max(1, self.num_heads_q // max(1, self.num_heads_kv)))
         self._row_lens = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
         self._row_map = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
+        self._identity = torch.arange(self.max_rows, dtype=torch.int32, device=device)
 
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
               fast_build: bool = False) -> B200PagedAttentionMetadata:
+        """Runs eagerly before every step (and before every CUDA-graph replay).  The kernels a FULL graph captured read
+        their row lengths and row map from the builder's OWN fixed buffers, whatever the batch looks like: a pure-decode
+        batch fills them with (seq_lens, identity), a batch with multi-token requests with the expanded rows.  Which of
+        the two it is therefore never changes a pointer baked into a captured launch."""
         m = common_attn_metadata
         T = m.num_actual_tokens
         if T > self.max_rows:
             raise B200AttnError(f"{T} tokens exceed the planned maximum of {self.max_rows}")
         if m.max_query_len <= 1 and T == m.num_reqs:
-            seq_lens, row_map = m.seq_lens, None                    # pure decode: rows == requests
+            self._row_lens[:T].copy_(m.seq_lens[:T])                # pure decode: rows == requests
+            self._row_map[:T].copy_(self._identity[:T])
         else:
             lens, rmap = expand_query_rows(m.query_start_loc, m.seq_lens, T)
             self._row_lens[:T].copy_(lens)
             self._row_map[:T].copy_(rmap)
-            seq_lens, row_map = self._row_lens[:T], self._row_map[:T]
-        self.workspace.make_plan(seq_lens, self.num_heads_q, self.num_heads_kv)
+        seq_lens, row_map = self._row_lens[:T], self._row_map[:T]
+        self.workspace.make_plan(seq_lens, self.num_heads_q, self.num_heads_kv, m.block_table_tensor, self.block_size, row_map)
         return B200PagedAttentionMetadata(
             num_actual_tokens=T, num_rows=T, max_query_len=m.max_query_len, seq_lens=seq_lens,
             block_table=m.block_table_tensor, row_map=row_map, slot_mapping=m.slot_mapping, workspace=self.workspace)
@@ -213,7 +219,11 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
 
 
 class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
-    can_return_lse_for_decode: bool = True   # b200attn_decode writes natural-log LSE (DCP combine, §8e)
+    # vLLM's decode-context-parallel gate ($VLLM/v1/worker/cp_utils.py:31) asserts on this flag and would then call forward()
+    # with rank-local block tables and GLOBAL seq_lens.  forward() does not run that flow (query all-gather, local lengths,
+    # LSE combine), so the flag stays off and __init__ refuses a DCP group; the sequence-split exchange of this repo is
+    # driven explicitly through forward_with_lse + parallel.PeerExchange / dcp_combine instead.
+    can_return_lse_for_decode: bool = False
 
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int | None = None,
                  alibi_slopes: list[float] | None = None, sliding_window: int | None = None,
@@ -233,6 +243,8 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
             raise NotImplementedError("B200 paged attention: decoder self-attention only")
         if head_size != 128:
             raise NotImplementedError(f"B200 paged attention: head_size {head_size} unsupported (128 only)")
+        if getattr(self, "dcp_world_size", 1) > 1:   # set by AttentionImplBase.__new__ ($VLLM/v1/attention/backend.py:731-757)
+            raise NotImplementedError("B200 paged attention: vLLM decode-context-parallel groups are not supported")
         if kv_cache_dtype not in B200PagedAttentionBackend.supported_kv_cache_dtypes:
             raise NotImplementedError(f"B200 paged attention: kv_cache_dtype {kv_cache_dtype!r} unsupported")
         self.num_heads = num_heads
@@ -330,6 +342,8 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         T = md.num_actual_tokens
         k_cache, v_cache = self._planes(kv_cache)
         k_scale, v_scale = self._scales(layer, query.device)
+        # rows that hold no token on this rank come back as (o = 0, lse = -inf) from the kernel itself (decode_tc.cu /
+        # decode.cu write them when an LSE buffer is given), so a stale buffer can never leak into the combine
         md.workspace.decode(query[:T].view(T, self.num_heads, self.head_size), k_cache, v_cache, md.block_table,
                             md.seq_lens, output[:T].view(T, self.num_heads, self.head_size), k_scale, v_scale,
                             self.scale, lse=lse, row_map=md.row_map, fresh_tokens=max(1, md.max_query_len))

@@ -15,6 +15,7 @@ static int g_opt_pdl = 1;
 static int g_opt_force_simt = 0;
 static int g_opt_debug = 0;
 static int g_opt_tc = 1;
+static int g_opt_cluster = 2;   // thread-block cluster size of the tcgen05 decode kernel (1 = no clusters)
 static unsigned long long* g_dbg_buf = nullptr;
 
 void set_error(const char* fmt, ...) {
@@ -34,21 +35,37 @@ int check_cuda(cudaError_t e, const char* what) {
 int option_force_simt() { return g_opt_force_simt; }
 int option_debug() { return g_opt_debug; }
 int option_tc() { return g_opt_tc; }
+int option_cluster() { return g_opt_cluster; }
 unsigned long long* option_debug_buffer() { return g_dbg_buf; }
 
-int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args) {
+int launch_with_pdl_cluster(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args, int cluster) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid;
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (g_opt_pdl) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = (unsigned)cluster;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = g_opt_pdl ? 1 : 0;
+  cfg.numAttrs = n;
   return check_cuda(cudaLaunchKernelExC(&cfg, func, args), "cudaLaunchKernelExC");
+}
+
+int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args) {
+  return launch_with_pdl_cluster(func, grid, block, smem, stream, args, 1);
 }
 
 // ---- cuTensorMapEncodeTiled via the runtime's driver entry point lookup ----
@@ -136,6 +153,7 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
   else if (!strcmp(name, "force_simt")) slot = &g_opt_force_simt;
   else if (!strcmp(name, "debug")) slot = &g_opt_debug;
   else if (!strcmp(name, "tc")) slot = &g_opt_tc;
+  else if (!strcmp(name, "cluster")) slot = &g_opt_cluster;
   if (!slot) {
     set_error("set_option: unknown option '%s'", name);
     return B200ATTN_EINVAL;
@@ -146,6 +164,6 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
 }
 
 // debug only: device buffer of [num_ctas][8] uint64 that the decode kernel fills with %globaltimer stamps
-extern "C" __attribute__((visibility("default"))) void b200attn_debug_set_timeline_buffer(void* dev_ptr) {
+extern "C" void b200attn_debug_set_timeline_buffer(void* dev_ptr) {
   g_dbg_buf = reinterpret_cast<unsigned long long*>(dev_ptr);
 }

@@ -23,14 +23,20 @@ constexpr int kMaxGrid = 1024;                                // plan capacity (
 constexpr int kMaxGroup = B200ATTN_MAX_GROUP;                 // q heads per kv head per CTA pass
 static_assert(kTileTokens == B200ATTN_TILE_TOKENS, "header / kernel tile mismatch");
 
-// Plan buffer layout (int32 words):
-//   [0] total_tiles  [1] tiles_per_cta  [2] grid  [3] num_seqs  [4] num_kv_heads (virtual)  [5..7] 0
-//   [8 .. 8+kMaxGrid*4)         int4 cta_start[kMaxGrid] = {seq, kv_head, tile, n_tiles}  (seq=-1: idle)
+// Plan buffer layout (int32 words), ABI version 3:
+//   [0] total_tiles  [1] tiles_per_cta  [2] grid  [3] num_seqs  [4] num_kv_heads (virtual)  [5] chunks per cache block  [6..7] 0
+//   [8 .. 8+kMaxGrid*64)        one 256-byte ENTRY per persistent CTA, everything its first TMA needs in one coalesced load:
+//        [0] seq (-1: idle) [1] kv head (virtual) [2] first 64-token tile [3] tile count
+//        [4] seq_len of that row [5] block-table row (row_map[seq] or seq) [6] tile prefix of seq [7] tiles_per_cta
+//        [8] grid [9] num_seqs (both checked against the launch: a plan / launch mismatch traps instead of reading garbage)
+//        [32..64) block ids of the first 32 16-token chunks of the CTA's first segment (chunk = tile * 4 + j)
 //   [.. +kMaxGrid*4)            counters of the in-kernel merge, one (ticket, published) pair per (first CTA, slot) of a
 //                               split (sequence, kv head) pair; zeroed by the plan kernel, self-resetting afterwards
 //   [.. +B+1)                   tile_prefix[num_seqs+1] (exclusive scan of ceil(L/64))
 constexpr int kPlanHeaderWords = 8;
-constexpr int kPlanCtaWords = kMaxGrid * 4;
+constexpr int kPlanEntryWords = 64;
+constexpr int kPlanEntryIds = 32;
+constexpr int kPlanCtaWords = kMaxGrid * kPlanEntryWords;
 constexpr int kPlanCounterOffset = kPlanHeaderWords + kPlanCtaWords;
 constexpr int kPlanCounterWords = kMaxGrid * 4;   // [0, 2*kMaxGrid): arrival tickets, [2*kMaxGrid, 4*kMaxGrid): published partials
 constexpr int kPlanPrefixOffset = kPlanCounterOffset + kPlanCounterWords;
@@ -99,12 +105,62 @@ __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
 }
 
+// Thread-block cluster / distributed shared memory
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local_addr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_cluster_f32x2(uint32_t addr, float a, float b) {
+  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+// arrive (count 1) on an mbarrier in another CTA of the cluster; release at cluster scope orders this thread's earlier
+// (and, through CTA barriers, its CTA's earlier) distributed-shared-memory stores before it
+__device__ __forceinline__ void mbar_arrive_remote_release(uint32_t remote_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_acq_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
 // Programmatic dependent launch (no-ops when the kernel was launched without the attribute).
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+// non-blocking arrival on a named barrier other warps bar.sync on (`threads` = total participants, arrivers included)
+__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
 }
 
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {

@@ -93,6 +93,12 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) dbg_stamp(p, 0);
+  // the CTA's plan entry: requested first, so its latency hides behind the barrier set-up
+  const int32_t* ent = p.plan + kPlanHeaderWords + (size_t)blockIdx.x * kPlanEntryWords;
+  const int4 cs = __ldg(reinterpret_cast<const int4*>(ent));
+  const int4 cx = __ldg(reinterpret_cast<const int4*>(ent) + 1);   // seq_len, block-table row, tile prefix of the first segment; tiles per CTA
+  const int4 chk = __ldg(reinterpret_cast<const int4*>(ent) + 2);
+  const int first_ids = warp == kConsumerWarps ? __ldg(ent + kPlanEntryIds + lane) : 0;   // producer: block ids of the first 8 tiles
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -116,7 +122,20 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   // Q, the newest tokens, `out`, the workspace and the merge counters are only touched after the wait.
   pdl_launch_dependents();
 
-  const int4 cs = __ldg(reinterpret_cast<const int4*>(p.plan + kPlanHeaderWords) + blockIdx.x);
+  if (chk.x != (int)gridDim.x || chk.y != p.B) __trap();   // plan / launch mismatch
+  // rows without any token: (o = 0, lse = -inf) when the caller wants the LSE (see decode_tc.cu); idle CTAs take part
+  if (p.lse_out != nullptr && warp < kConsumerWarps) {
+    using E = Elem<QDT>;
+    pdl_wait();
+    for (int s = blockIdx.x; s < p.B; s += gridDim.x) {
+      if (__ldg(p.seq_lens + s) > 0) continue;
+      for (int i = threadIdx.x; i < p.Hq * kD; i += kConsumerWarps * 32) {
+        const int hq = i / kD, d = i % kD;
+        reinterpret_cast<typename E::type*>(p.out)[(int64_t)s * p.out_stride_t + (int64_t)hq * p.out_stride_h + d] = E::from_float(0.f);
+      }
+      for (int hq = threadIdx.x; hq < p.Hq; hq += kConsumerWarps * 32) p.lse_out[(int64_t)s * p.Hq + hq] = -INFINITY;
+    }
+  }
   if (cs.x < 0 || cs.w <= 0) return;  // idle CTA (fewer tiles than CTAs)
   if (threadIdx.x == 0) dbg_stamp(p, 1);
 
@@ -129,13 +148,14 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     bool waited = false;
     int early_left = p.fresh >= 0 ? kStages : 0;  // tiles we may still issue before the wait (ring is empty at start)
     while (remaining > 0) {
-      const int L = max(__ldg(p.seq_lens + s), 0);
+      // the first segment's metadata comes with the plan entry (no dependent loads before the first TMA)
+      const int L = sg == 0 ? cx.x : max(__ldg(p.seq_lens + s), 0);
       const int nt = (L + kTileTokens - 1) / kTileTokens;
       const int n = min(remaining, nt - tile);
       const int kvh = hv / p.gsplit;
-      const int row = p.row_map ? __ldg(p.row_map + s) : s;
+      const int row = sg == 0 ? cx.y : (p.row_map ? __ldg(p.row_map + s) : s);
       const int32_t* bt = p.block_table + (int64_t)row * p.bt_stride;
-      const int pfx = __ldg(p.plan + kPlanPrefixOffset + s);
+      const int pfx = sg == 0 ? cx.z : __ldg(p.plan + kPlanPrefixOffset + s);
       const uint32_t slot = sg & 1;
       bool q_issued = false;
       int blk = 0;
@@ -166,7 +186,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
         const int tl = tile + tt;
         if ((tt & 7) == 0) {  // refill 32 block ids (8 tiles) with one coalesced load
           const int ci = (tl << 2) + lane;
-          blk = (ci * kChunkTokens < L) ? __ldg(bt + ci / p.cpb) : 0;
+          blk = (sg == 0 && tt == 0) ? first_ids : ((ci * kChunkTokens < L) ? __ldg(bt + ci / p.cpb) : 0);
         }
         mbar_wait(empty_bar(stage), phase ^ 1);
         const int tok0 = tl * kTileTokens;
@@ -536,19 +556,21 @@ int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaSt
 int option_force_simt();
 int option_debug();
 int option_tc();
-int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, int q_dtype, cudaStream_t stream);
+int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, DecodeParams& p, int grid, int q_dtype, cudaStream_t stream);
 unsigned long long* option_debug_buffer();
 
 template <int KVT, int QDT, int NT>
 static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, cudaStream_t stream) {
   using SM = Smem<KVT, NT>;
   auto fn = decode_kernel<KVT, QDT, NT>;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static bool configured[64] = {};  // per instantiation and device (the attribute belongs to the context)
+  int dev = 0;
+  if (check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return B200ATTN_ECUDA;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
     if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kTotalBytes),
                    "cudaFuncSetAttribute(decode smem)"))
       return B200ATTN_ECUDA;
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   void* args[] = {(void*)&tk, (void*)&tv, (void*)&p};
   return launch_with_pdl((const void*)fn, dim3(grid), dim3(kDecodeThreads), SM::kTotalBytes, stream, args);
@@ -649,6 +671,7 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stri
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.B = num_seqs; p.Hq = num_q_heads; p.Hv = num_kv_heads * gsplit; p.G = G; p.gsplit = gsplit;
   p.cpb = block_size / kChunkTokens;
+  p.cluster = 1;
   p.debug = option_debug();
   p.dbg = option_debug_buffer();
 

@@ -28,17 +28,20 @@ struct DecodeParams {
   int cpb;              // 16-token chunks per cache block (block_size / 16)
   int fresh;            // trailing positions of a row the preceding kernel may have written (< 0: unknown, no early prefetch)
   int fused_merge;      // 1: the last CTA to finish a split (sequence, kv head) pair merges its partials in-kernel
-  unsigned long long* dbg;  // debug timeline buffer [grid][8] (globaltimer ns) or nullptr
+  int cluster;          // thread-block cluster size of this launch (1: none); partials of a pair whose CTAs share a cluster
+                        // are folded through distributed shared memory instead of the L2 workspace
+  unsigned long long* dbg;  // debug timeline buffer [grid][16] (globaltimer ns) or nullptr
   int debug;            // bit0: consumers skip the math (pure streaming ceiling); never set in production
 };
 
 constexpr int kD = 128;
+constexpr int kDbgSlots = 16;
 
 __device__ __forceinline__ void dbg_stamp(const DecodeParams& p, int slot) {
   if (p.dbg != nullptr) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    p.dbg[(size_t)blockIdx.x * 8 + slot] = t;
+    p.dbg[(size_t)blockIdx.x * kDbgSlots + slot] = t;
   }
 }
 
@@ -58,6 +61,21 @@ __device__ __forceinline__ float q_to_float(uint16_t raw) {
 //      partials (one L2 round trip, all loads in flight at once) and combines them with its registers.
 // Both counters live in the plan buffer (zeroed by the plan kernel, re-armed here by the last CTA).  mrg = smem scratch of
 // 64 floats, hand = 3 ints of smem.
+// Where the pieces of a split (sequence, virtual kv head) pair live: CTAs c_lo..c_hi, the first one's workspace slot.
+struct MergeLoc {
+  int c_lo, c_hi, slot_lo, np;
+};
+__device__ __forceinline__ MergeLoc merge_locate(int Hv, int tpc, int hv, int L, int pfx) {
+  MergeLoc m;
+  const int nt = (L + kTileTokens - 1) / kTileTokens;
+  const long long x0 = (long long)pfx * Hv + (long long)hv * nt;
+  m.c_lo = (int)(x0 / tpc);
+  m.c_hi = (int)((x0 + nt - 1) / tpc);
+  m.slot_lo = (x0 == (long long)m.c_lo * tpc) ? 0 : 1;
+  m.np = m.c_hi - m.c_lo + 1;
+  return m;
+}
+
 // Ticket of the in-kernel merge (one thread): where the pair's counters are and in which order this CTA arrived.
 struct MergeTicket {
   int* cnt;       // arrival counter; the "published" counter sits kPlanCounterWords / 2 words further

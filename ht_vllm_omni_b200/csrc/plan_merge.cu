@@ -15,7 +15,8 @@ namespace b200attn {
 // CTA c owns x in [c * tpc, min((c + 1) * tpc, total)).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ seq_lens, int B, int Hv, int grid,
-                                                   int32_t* __restrict__ plan) {
+                                                   const int32_t* __restrict__ block_table, int64_t bt_stride,
+                                                   const int32_t* __restrict__ row_map, int cpb, int32_t* __restrict__ plan) {
   __shared__ int warp_sums[8];
   __shared__ int carry_s;
   // No early griddepcontrol.launch_dependents here: kernels that follow may read the plan BEFORE their own
@@ -59,13 +60,15 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
     plan[2] = grid;
     plan[3] = B;
     plan[4] = Hv;
-    plan[5] = plan[6] = plan[7] = 0;
+    plan[5] = cpb;
+    plan[6] = plan[7] = 0;
   }
   __syncthreads();  // prefix[] (global) written by this CTA is visible to it after the barrier
-  int4* cta = reinterpret_cast<int4*>(plan + kPlanHeaderWords);
+  int32_t* ent = plan + kPlanHeaderWords;
   for (int c = tid; c < grid; c += 256) {
     const long long x = (long long)c * tpc;
     int4 e = make_int4(-1, 0, 0, 0);
+    int L = 0, row = 0, pfx = 0;
     if (x < total) {
       // largest s with Hv * prefix[s] <= x  (prefix is non-decreasing; empty sequences repeat a value,
       // taking the largest index lands on the sequence that owns x)
@@ -75,15 +78,34 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
         if ((long long)prefix[mid] * Hv <= x) lo = mid; else hi = mid;
       }
       const int s = lo;
-      const int nt = prefix[s + 1] - prefix[s];
-      const long long r = x - (long long)prefix[s] * Hv;
+      pfx = prefix[s];
+      const int nt = prefix[s + 1] - pfx;
+      const long long r = x - (long long)pfx * Hv;
       e.x = s;
       e.y = (int)(r / nt);
       e.z = (int)(r % nt);
       const long long left = total - x;
       e.w = (int)(left < tpc ? left : tpc);
+      L = max(seq_lens[s], 0);
+      row = row_map ? row_map[s] : s;
     }
-    cta[c] = e;
+    int32_t* d = ent + (size_t)c * kPlanEntryWords;
+    *reinterpret_cast<int4*>(d) = e;
+    *reinterpret_cast<int4*>(d + 4) = make_int4(L, row, pfx, tpc);
+    *reinterpret_cast<int4*>(d + 8) = make_int4(grid, B, 0, 0);
+  }
+  __syncthreads();
+  // block ids of the first 32 16-token chunks of every CTA's first segment: the decode producer issues its first TMA
+  // loads after ONE dependent load (this entry) instead of plan -> seq_lens -> row_map -> block_table
+  for (int idx = tid; idx < grid * kPlanEntryIds; idx += 256) {
+    const int c = idx / kPlanEntryIds, j = idx % kPlanEntryIds;
+    const int32_t* d = ent + (size_t)c * kPlanEntryWords;
+    int id = 0;
+    if (d[0] >= 0) {
+      const int ci = d[2] * (kTileTokens / kChunkTokens) + j;
+      if (ci * kChunkTokens < d[4]) id = block_table[(int64_t)d[5] * bt_stride + ci / cpb];
+    }
+    ent[(size_t)c * kPlanEntryWords + kPlanEntryIds + j] = id;
   }
 }
 
@@ -293,8 +315,9 @@ extern "C" size_t b200attn_workspace_bytes(int32_t head_dim, int32_t num_ctas) {
 }
 
 extern "C" int b200attn_decode_plan(const int32_t* seq_lens, int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads,
-                                    int32_t num_ctas, void* plan, size_t plan_bytes, void* stream) {
-  if (!seq_lens || !plan) {
+                                    int32_t num_ctas, const int32_t* block_table, int64_t block_table_stride,
+                                    const int32_t* row_map, int32_t block_size, void* plan, size_t plan_bytes, void* stream) {
+  if (!seq_lens || !plan || !block_table) {
     set_error("decode_plan: null pointer argument");
     return B200ATTN_EINVAL;
   }
@@ -307,13 +330,17 @@ extern "C" int b200attn_decode_plan(const int32_t* seq_lens, int32_t num_seqs, i
     set_error("decode_plan: num_ctas %d out of range (1..%d)", num_ctas, kMaxGrid);
     return B200ATTN_EINVAL;
   }
+  if (block_size <= 0 || block_size % kChunkTokens != 0) {
+    set_error("decode_plan: block_size %d must be a positive multiple of %d", block_size, kChunkTokens);
+    return B200ATTN_EINVAL;
+  }
   if (plan_bytes < b200attn_plan_bytes(num_seqs)) {
     set_error("decode_plan: plan buffer too small (%zu < %zu)", plan_bytes, b200attn_plan_bytes(num_seqs));
     return B200ATTN_ENOSPACE;
   }
-  int B = num_seqs, Hv = num_kv_heads * gsplit, grid = num_ctas;
+  int B = num_seqs, Hv = num_kv_heads * gsplit, grid = num_ctas, cpb = block_size / kChunkTokens;
   int32_t* pl = reinterpret_cast<int32_t*>(plan);
-  void* args[] = {(void*)&seq_lens, &B, &Hv, &grid, &pl};
+  void* args[] = {(void*)&seq_lens, &B, &Hv, &grid, (void*)&block_table, &block_table_stride, (void*)&row_map, &cpb, &pl};
   return launch_with_pdl((const void*)plan_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(stream), args);
 }
 

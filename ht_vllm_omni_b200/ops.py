@@ -41,11 +41,17 @@ def _require_cuda(*ts: torch.Tensor) -> None:
             raise B200AttnError("b200attn ops need CUDA tensors: there is no CPU fallback for this path")
 
 
-def _scale_stride(scale: torch.Tensor, num_kv_heads: int) -> int:
+def _scale_stride(scale: torch.Tensor, num_kv_heads: int, other: torch.Tensor | None = None) -> int:
+    """Element stride of the per-tensor (0) / per-head (1) scale vectors.  The kernels apply ONE stride to k_scale and
+    v_scale, so `other` (the second scale) must have the same number of elements."""
     n = scale.numel()
+    if other is not None and other.numel() != n:
+        raise B200AttnError(f"k_scale and v_scale must have the same number of elements ({n} vs {other.numel()})")
+    if scale.dtype != torch.float32 or (other is not None and other.dtype != torch.float32):
+        raise B200AttnError("kv scales must be fp32")
     if n == 1:
         return 0
-    if n == num_kv_heads and scale.is_contiguous():
+    if n == num_kv_heads and scale.is_contiguous() and (other is None or other.is_contiguous()):
         return 1
     raise B200AttnError(f"kv scale must have 1 or Hkv={num_kv_heads} contiguous elements, got shape {tuple(scale.shape)}")
 
@@ -92,7 +98,7 @@ def kv_write(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_ca
     Hkv, D = key.shape[1], key.shape[2]
     sb, ss, sh = _cache_strides(k_cache, v_cache)
     kvdt = _dt(k_cache)
-    sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
+    sstride = _scale_stride(k_scale, Hkv, v_scale) if kvdt == DT_FP8_E4M3 else 0
     check(lib.b200attn_kv_write(
         key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1), value.stride(0), value.stride(1),
         k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, slot_mapping.data_ptr(), T, Hkv, D, k_cache.shape[1],
@@ -130,7 +136,7 @@ def rope_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, p
     Hq, Hkv, D = query.shape[1], key.shape[1], key.shape[2]
     sb, ss, sh = _cache_strides(k_cache, v_cache)
     kvdt = _dt(k_cache)
-    sstride = _scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0
+    sstride = _scale_stride(k_scale, Hkv, v_scale) if kvdt == DT_FP8_E4M3 else 0
     check(lib.b200attn_rope_kv_write(
         query.data_ptr(), query.stride(0), query.stride(1), Hq, key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1),
         value.stride(0), value.stride(1), positions.data_ptr(), cos_sin_cache.data_ptr(), cos_sin_cache.shape[1], (1 if is_neox else 0) | (2 if round_each_op else 0),
@@ -147,34 +153,44 @@ def _(query, key, value, positions, cos_sin_cache, is_neox, k_cache, v_cache, sl
 # decode_plan (once per step) and paged_decode (= split-KV decode kernel + merge kernel)
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("b200attn::decode_plan", mutates_args=("plan",), device_types="cuda")
-def decode_plan(seq_lens: torch.Tensor, plan: torch.Tensor, num_q_heads: int, num_kv_heads: int, num_ctas: int) -> None:
-    _require_cuda(seq_lens, plan)
+def decode_plan(seq_lens: torch.Tensor, plan: torch.Tensor, num_q_heads: int, num_kv_heads: int, num_ctas: int,
+                block_table: torch.Tensor, block_size: int, row_map: torch.Tensor) -> None:
+    """`block_table` / `block_size` / `row_map` (EMPTY = identity) are the step metadata the decode calls of this step will
+    get: the plan copies each CTA's first block ids into its entry (include/b200attn.h)."""
+    _require_cuda(seq_lens, plan, block_table)
     if seq_lens.dtype != torch.int32 or plan.dtype != torch.int32 or not seq_lens.is_contiguous():
         raise B200AttnError("seq_lens and plan must be contiguous int32")
+    if block_table.dtype != torch.int32 or block_table.dim() != 2 or block_table.stride(1) != 1:
+        raise B200AttnError("block_table must be int32 [rows, max_blocks] with contiguous rows")
+    rm = row_map if row_map.numel() > 0 else None
+    if rm is not None and (rm.dtype != torch.int32 or not rm.is_contiguous() or rm.shape[0] != seq_lens.shape[0]):
+        raise B200AttnError("row_map must be contiguous int32 [num_rows]")
     check(load_library().b200attn_decode_plan(seq_lens.data_ptr(), seq_lens.shape[0], num_q_heads, num_kv_heads, num_ctas,
+                                              block_table.data_ptr(), block_table.stride(0),
+                                              rm.data_ptr() if rm is not None else None, int(block_size),
                                               plan.data_ptr(), plan.numel() * 4, _stream(plan)), "b200attn_decode_plan")
 
 
 @decode_plan.register_fake
-def _(seq_lens, plan, num_q_heads, num_kv_heads, num_ctas) -> None:
+def _(seq_lens, plan, num_q_heads, num_kv_heads, num_ctas, block_table, block_size, row_map) -> None:
     return None
 
 
-def _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale):
+def _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale):
     if query.dim() != 3 or out.dim() != 3 or query.stride(2) != 1 or out.stride(2) != 1 or query.dtype != out.dtype:
         raise B200AttnError("query/out must be [B, Hq, D] of the same dtype with contiguous head_dim")
     if block_table.dtype != torch.int32 or seq_lens.dtype != torch.int32 or block_table.stride(1) != 1:
         raise B200AttnError("block_table / seq_lens must be int32 (block_table rows contiguous)")
     Hkv = k_cache.shape[2]
     kvdt = _dt(k_cache)
-    return _cache_strides(k_cache, v_cache), kvdt, (_scale_stride(k_scale, Hkv) if kvdt == DT_FP8_E4M3 else 0)
+    return _cache_strides(k_cache, v_cache), kvdt, (_scale_stride(k_scale, Hkv, v_scale) if kvdt == DT_FP8_E4M3 else 0)
 
 
 def launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
                         num_ctas, lse=None, row_map=None, fresh_tokens=-1, fused_merge=False) -> None:
     """Kernel 2 (b200attn_decode): final rows for unsplit sequences; split ones leave (o, m, l) partials that are merged
     in-kernel by the last-arriving CTA (`fused_merge`) or by a following launch_merge."""
-    (sb, ss, sh), kvdt, sstride = _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale)
+    (sb, ss, sh), kvdt, sstride = _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale)
     if row_map is not None and (row_map.dtype != torch.int32 or not row_map.is_contiguous() or row_map.shape[0] != seq_lens.shape[0]):
         raise B200AttnError("row_map must be contiguous int32 [num_rows]")
     check(load_library().b200attn_decode(
@@ -295,11 +311,14 @@ class DecodeWorkspace:
             return self.num_ctas
         return aligned_grid(self.num_ctas, num_seqs, num_q_heads, num_kv_heads)
 
-    def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int) -> None:
+    def make_plan(self, seq_lens: torch.Tensor, num_q_heads: int, num_kv_heads: int, block_table: torch.Tensor,
+                  block_size: int, row_map: torch.Tensor | None = None) -> None:
+        """Once per step (shared by all layers).  `block_table` / `row_map` must be the tensors `decode` gets afterwards."""
         if seq_lens.shape[0] > self.max_num_seqs:
             raise B200AttnError(f"batch {seq_lens.shape[0]} exceeds planned max_num_seqs {self.max_num_seqs}")
         self.grid = self.grid_for(seq_lens.shape[0], num_q_heads, num_kv_heads)
-        torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.grid)
+        torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.grid, block_table, block_size,
+                                       self._no_map if row_map is None else row_map)
 
     def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None,
                row_map=None, fresh_tokens: int = -1, fused_merge: bool = True) -> None:

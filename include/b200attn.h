@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 2
+#define B200ATTN_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -123,16 +123,24 @@ B200ATTN_API int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t
  *   ($VLLM/v1/attention/backends/flashinfer.py:886-1248 `plan`, triton_attn.py:216-268).
  *
  * Cuts the flat list of (sequence, kv head, 64-token tile) work items into equal contiguous
- * ranges, one per persistent CTA, entirely on the device (no host sync, capture-safe).
+ * ranges, one per persistent CTA, entirely on the device (no host sync, capture-safe), and copies into
+ * each CTA's 256-byte plan entry everything its first TMA load needs (sequence length, block-table row,
+ * the first 32 block ids), so a decode CTA starts streaming after ONE dependent load.
+ * `block_table` / `block_table_stride` / `row_map` (nullable) / `block_size` must be the ones later given to
+ * b200attn_decode (the step's metadata: the same for every layer).
  * `plan` must hold b200attn_plan_bytes(num_seqs) bytes.  `num_ctas` is the decode grid: use
  * b200attn_default_ctas(kv_dtype) (2 CTAs/SM); tests pass small values
- * to force many split points.  The SAME num_ctas must be given to decode and merge.
+ * to force many split points.  The SAME num_ctas must be given to decode and merge (the decode kernel traps on a
+ * plan built for another grid or batch).
  */
 B200ATTN_API size_t b200attn_plan_bytes(int32_t max_num_seqs);
 B200ATTN_API int b200attn_default_ctas(int32_t kv_dtype);
 B200ATTN_API int b200attn_decode_plan(const int32_t* seq_lens, int32_t num_seqs,
                          int32_t num_q_heads, int32_t num_kv_heads,
-                         int32_t num_ctas, void* plan, size_t plan_bytes, void* stream);
+                         int32_t num_ctas,
+                         const int32_t* block_table, int64_t block_table_stride,
+                         const int32_t* row_map /* nullable, [num_seqs] */, int32_t block_size,
+                         void* plan, size_t plan_bytes, void* stream);
 
 /* Bytes of split-KV workspace (partial o, m, l) the decode + merge kernels need. */
 B200ATTN_API size_t b200attn_workspace_bytes(int32_t head_dim, int32_t num_ctas);
@@ -229,11 +237,20 @@ B200ATTN_API int b200attn_kv_gather(const void* const* k_planes, const void* con
                        int32_t block_size, int32_t row_bytes, void* out, void* stream);
 
 /*
- * Runtime knobs (host, process-wide): "pdl" (programmatic dependent launch, default 1),
- * "force_simt" (route every group size to the CUDA-core consumer, default 0).
+ * Runtime knobs (host, process-wide): "pdl" (programmatic dependent launch, default 1), "tc" (tcgen05 consumer for
+ * fp8 KV with group size <= 8, default 1), "cluster" (thread-block cluster size of that kernel: partials of a split
+ * pair whose CTAs share a cluster are merged through distributed shared memory; default 2, 1 = off).
  * Returns the previous value or B200ATTN_EINVAL for an unknown name.
  */
 B200ATTN_API int b200attn_set_option(const char* name, int32_t value);
+
+/*
+ * Debug only (tests/tools/timeline*.py): a DEVICE buffer of [num_ctas][8] uint64 that the next decode launches fill with
+ * %globaltimer stamps (CTA entry, set-up done, first TMA, first tile, last tile, exit, publish / merge time).  While a
+ * buffer is set, b200attn_decode launches the instrumented instantiation of the kernel; NULL (the default) restores the
+ * production one, which carries no instrumentation at all.
+ */
+B200ATTN_API void b200attn_debug_set_timeline_buffer(void* dev_ptr);
 
 #ifdef __cplusplus
 }

@@ -65,9 +65,9 @@ def test_only_sm100a_code_is_embedded():
 
 
 def test_version_and_geometry(lib):
-    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 2
+    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 3
     assert _lib.TILE_TOKENS == 64 and _lib.MAX_GROUP == 16
-    assert lib.b200attn_plan_bytes(64) >= (8 + 1024 * 4 + 1024 * 2 + 65) * 4
+    assert lib.b200attn_plan_bytes(64) >= (8 + 1024 * 64 + 1024 * 4 + 65) * 4   # header, 256-byte CTA entries, merge counters, prefix
     assert lib.b200attn_plan_bytes(64) % 16 == 0
     # workspace = [ctas][2][16][D] fp32 partial outputs + [ctas][2][16][2] fp32 (m, l)
     assert lib.b200attn_workspace_bytes(128, 296) == (296 * 2 * 16 * 128 + 296 * 2 * 16 * 2) * 4
@@ -79,12 +79,14 @@ def test_argument_errors_are_codes_not_exceptions(lib):
     # null pointers -> EINVAL with a message (validated before any CUDA call, so this works without a device)
     rc = lib.b200attn_kv_write(None, None, 0, 0, 0, 0, None, None, 0, 0, 0, None, 4, 2, 128, 16, 0, 2, None, None, 0, None)
     assert rc == -1 and b"null pointer" in lib.b200attn_last_error()
-    rc = lib.b200attn_decode_plan(None, 4, 16, 2, 8, None, 0, None)
+    rc = lib.b200attn_decode_plan(None, 4, 16, 2, 8, None, 0, None, 16, None, 0, None)
     assert rc == -1
     buf = (C.c_int32 * 16)()
-    rc = lib.b200attn_decode_plan(buf, 4, 16, 3, 8, buf, 64, None)  # Hq % Hkv != 0
+    rc = lib.b200attn_decode_plan(buf, 4, 16, 3, 8, buf, 4, None, 16, buf, 64, None)  # Hq % Hkv != 0
     assert rc == -1 and b"bad shape" in lib.b200attn_last_error()
-    rc = lib.b200attn_decode_plan(buf, 4, 16, 2, 8, buf, 64, None)  # plan buffer too small
+    rc = lib.b200attn_decode_plan(buf, 4, 16, 2, 8, buf, 4, None, 24, buf, 64, None)  # block_size not a multiple of 16
+    assert rc == -1 and b"block_size" in lib.b200attn_last_error()
+    rc = lib.b200attn_decode_plan(buf, 4, 16, 2, 8, buf, 4, None, 16, buf, 64, None)  # plan buffer too small
     assert rc == -3
     # empty batches are a successful no-op everywhere
     assert lib.b200attn_kv_write(None, None, 0, 0, 0, 0, None, None, 0, 0, 0, None, 0, 2, 128, 16, 0, 2, None, None, 0, None) == 0

@@ -155,3 +155,70 @@ def test_backend_under_cuda_graph_replay_with_changing_seq_lens():
         live = lens > 0
         err = np.abs(got[live] - ref[live])
         assert np.all(err <= 1e-2 + np.maximum(np.abs(ref[live]), 2.0 ** -14) * 2.0 ** -7), float(err.max())
+
+
+def test_full_graph_captures_forward_only_and_build_runs_eagerly_before_each_replay():
+    """vLLM's FULL-cudagraph flow: `build()` runs eagerly before every replay, only the layer hooks are inside
+    the graph.  One graph per token count serves BOTH a batch with multi-token requests and a pure-decode batch of the same
+    size, so the captured kernels must read their row lengths / row map from buffers that do not depend on which of the two
+    the batch is.  Capture on a mixed batch (3 requests, q_lens 2+1+1), replay on a pure-decode batch (4 requests), then on
+    the mixed batch again."""
+    from ht_vllm_omni_b200 import backend as B
+
+    be = B.B200PagedAttentionBackend
+    Hq, Hkv, D, bs, T, R = 16, 2, 128, 16, 4, 4
+    impl = be.get_impl_cls()(Hq, D, D ** -0.5, Hkv, None, None, "fp8")
+    layer = types.SimpleNamespace(_k_scale=torch.tensor([0.02], device="cuda"), _v_scale=torch.tensor([0.02], device="cuda"))
+    max_lens = np.array([700, 300, 1500, 64], np.int32)
+    bt_np, nb = O.make_block_table(max_lens, bs, seed=4)
+    kv_cache = _alloc_like_vllm(be, nb, bs, Hkv, D, "fp8", torch.uint8)
+    rng = np.random.default_rng(1)
+    kc_o = rng.integers(0, 0x78, (nb, bs, Hkv, D), dtype=np.uint8); vc_o = rng.integers(0, 0x78, (nb, bs, Hkv, D), dtype=np.uint8)
+    kv_cache[:, 0].copy_(torch.from_numpy(kc_o)); kv_cache[:, 1].copy_(torch.from_numpy(vc_o))
+    # persistent runner buffers (capture and replay see the same addresses)
+    d_seq = torch.zeros(R, dtype=torch.int32, device="cuda"); d_bt = torch.from_numpy(bt_np).cuda()
+    d_qsl = torch.zeros(R + 1, dtype=torch.int32, device="cuda")
+    d_slots = torch.full((T,), -1, dtype=torch.int64, device="cuda")
+    q = torch.randn(T, Hq * D, generator=torch.Generator().manual_seed(2)).to(torch.bfloat16).cuda()
+    kvn = torch.zeros(T, Hkv * D, dtype=torch.bfloat16, device="cuda")
+    out = torch.zeros(T, Hq * D, dtype=torch.bfloat16, device="cuda")
+    builder = be.get_builder_cls()(types.SimpleNamespace(block_size=bs, dtype=torch.uint8), ["l0"], _cfg(Hq, Hkv, D, 64), torch.device("cuda"))
+
+    def metadata(seq, q_lens):
+        n = len(seq)
+        qsl = np.concatenate([[0], np.cumsum(q_lens)]).astype(np.int32)
+        d_seq[:n].copy_(torch.from_numpy(np.asarray(seq, np.int32))); d_qsl[:n + 1].copy_(torch.from_numpy(qsl))
+        return vb.CommonAttentionMetadata(query_start_loc=d_qsl[:n + 1], query_start_loc_cpu=torch.from_numpy(qsl), seq_lens=d_seq[:n],
+                                          num_reqs=n, num_actual_tokens=T, max_query_len=int(max(q_lens)), max_seq_len=2048,
+                                          block_table_tensor=d_bt[:n], slot_mapping=d_slots)
+
+    def reference(seq, q_lens):
+        row_req = np.repeat(np.arange(len(seq)), q_lens)
+        row_len = np.concatenate([seq[r] - q_lens[r] + 1 + np.arange(q_lens[r]) for r in range(len(seq))]).astype(np.int32)
+        return O.paged_decode_exact(q.view(T, Hq, D).float().cpu().numpy(), kc_o, vc_o, bt_np[row_req], row_len, D ** -0.5,
+                                    np.array([0.02], np.float32), np.array([0.02], np.float32), fp8=True)
+
+    mixed = (np.array([700, 300, 1500]), np.array([2, 1, 1]))
+    pure = (np.array([650, 280, 1400, 64]), np.array([1, 1, 1, 1]))
+    md = builder.build(0, metadata(*mixed))
+
+    def hooks():
+        impl.do_kv_cache_update(layer, kvn, kvn, kv_cache, d_slots)     # all slots -1: writes nothing
+        impl.forward(layer, q, kvn, kvn, kv_cache, md, out)
+
+    s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        hooks()
+    torch.cuda.current_stream().wait_stream(s); torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        hooks()
+    for seq, q_lens in (pure, mixed, pure):
+        builder.build(0, metadata(seq, q_lens))     # eager, outside the graph -- as vLLM does
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        ref = reference(seq, q_lens)
+        got = out.view(T, Hq, D).float().cpu().numpy()
+        err = np.abs(got - ref)
+        assert np.all(err <= 1e-2 + np.maximum(np.abs(ref), 2.0 ** -14) * 2.0 ** -7), float(err.max())

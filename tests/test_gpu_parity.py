@@ -49,7 +49,7 @@ def run_case(ops, c, ctas=None, check_write=True, lse=False, fused_merge=True):
     ws = ops.DecodeWorkspace("cuda", c.B, torch.uint8 if c.fp8 else c.d_q.dtype, num_ctas=ctas)
     out = torch.full((c.B, c.Hq, c.D), float("nan"), dtype=c.d_q.dtype, device="cuda")
     d_lse = torch.zeros(c.B, c.Hq, dtype=torch.float32, device="cuda") if lse else None
-    ws.make_plan(c.d_lens, c.Hq, c.Hkv)
+    ws.make_plan(c.d_lens, c.Hq, c.Hkv, c.d_bt, c.bs)
     ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale, d_lse, fused_merge=fused_merge)
     torch.cuda.synchronize()
     got = out.float().cpu().numpy()
@@ -173,7 +173,7 @@ def test_golden_vectors_from_vllm_kernels(ops, golden, kind):
     for ctas in (1, 3, None):
         ws = ops.DecodeWorkspace(dev, B, dt, num_ctas=ctas)
         out = torch.zeros(B, Hq, D, dtype=torch.float16, device=dev)
-        ws.make_plan(lens, Hq, Hkv)
+        ws.make_plan(lens, Hq, Hkv, bt, kc.shape[1])
         ws.decode(q, kc, vc, bt, lens, out, ks, vs, float(g["sm_scale"]))
         torch.cuda.synchronize()
         got = out.float().cpu().numpy()
@@ -248,7 +248,7 @@ def test_strided_inputs_fused_qkv_slices(ops):
     out_big = torch.zeros(c.B + 3, c.Hq * c.D + 64, dtype=torch.bfloat16, device="cuda")
     out_view = out_big[:c.B, :c.Hq * c.D].view(c.B, c.Hq, c.D)
     ws = ops.DecodeWorkspace("cuda", c.B, torch.uint8, num_ctas=6)
-    ws.make_plan(c.d_lens, c.Hq, c.Hkv)
+    ws.make_plan(c.d_lens, c.Hq, c.Hkv, c.d_bt, c.bs)
     ws.decode(q_view, c.kc, c.vc, c.d_bt, c.d_lens, out_view, c.d_ks, c.d_vs, c.sm_scale)
     torch.cuda.synchronize()
     assert_close(out_view.float().cpu().numpy(), c.oracle_decode(kc_o, vc_o), "fp8", "bf16")
@@ -269,12 +269,51 @@ def test_padded_rows_and_stale_block_tables_are_never_dereferenced(ops):
     c.load_cache_from_np(kc_o, vc_o)
     ws = ops.DecodeWorkspace("cuda", c.B, torch.uint8, num_ctas=3)
     out = torch.full((c.B, c.Hq, c.D), 7.0, dtype=torch.bfloat16, device="cuda")
-    ws.make_plan(c.d_lens, c.Hq, c.Hkv)
+    ws.make_plan(c.d_lens, c.Hq, c.Hkv, bt, c.bs)       # the plan copies each CTA's first block ids: same table as decode
     ws.decode(c.d_q, c.kc, c.vc, bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale)
     torch.cuda.synchronize()
     valid = c.lens > 0
     assert_close(out.float().cpu().numpy(), c.oracle_decode(kc_o, vc_o), "fp8", "bf16", valid)
     assert float((out[1] - 7).abs().sum()) == 0 and float((out[3] - 7).abs().sum()) == 0   # padded rows untouched
+
+
+@pytest.mark.parametrize("kv", ["fp8", "bf16"])
+@pytest.mark.parametrize("ctas", [3, None])
+def test_rows_without_tokens_report_empty_partials_when_lse_is_requested(ops, kv, ctas):
+    """A sequence-split rank may hold no position of a short context (L < ranks): with an LSE buffer the kernel itself
+    writes (o = 0, lse = -inf) for such rows, so a combine by LSE never sees the previous layer's values (idle CTAs too)."""
+    c = Case([0, 130, 0, 0, 64, 0], 16, 2, kv=kv).cuda()
+    kc_o, vc_o = c.oracle_cache()
+    c.load_cache_from_np(kc_o, vc_o)
+    ws = ops.DecodeWorkspace("cuda", c.B, torch.uint8 if c.fp8 else torch.bfloat16, num_ctas=ctas)
+    out = torch.full((c.B, c.Hq, c.D), 7.0, dtype=torch.bfloat16, device="cuda")
+    lse = torch.full((c.B, c.Hq), 123.0, dtype=torch.float32, device="cuda")
+    ws.make_plan(c.d_lens, c.Hq, c.Hkv, c.d_bt, c.bs)
+    ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale, lse)
+    torch.cuda.synchronize()
+    empty = torch.from_numpy(c.lens == 0).cuda()
+    assert bool(torch.isneginf(lse[empty]).all()) and float(out[empty].abs().sum()) == 0
+    assert bool(torch.isfinite(lse[~empty]).all())
+    assert_close(out.float().cpu().numpy(), c.oracle_decode(kc_o, vc_o), kv, "bf16", c.lens > 0)
+
+
+def test_plan_for_another_grid_or_batch_traps_instead_of_reading_garbage(ops):
+    """a decode launched with a plan built for a different grid / batch must not run silently."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import torch, ht_vllm_omni_b200.ops as ops
+        from tests.helpers import Case
+        c = Case([300, 700], 16, 2, kv="fp8").cuda()
+        ws = ops.DecodeWorkspace("cuda", c.B, torch.uint8, num_ctas=6)
+        ws.make_plan(c.d_lens, c.Hq, c.Hkv, c.d_bt, c.bs)
+        out = torch.zeros(c.B, c.Hq, c.D, dtype=torch.bfloat16, device="cuda")
+        ws.grid = 4      # launch with another grid than the plan was cut for
+        ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale)
+        torch.cuda.synchronize()
+        print("NO-TRAP")
+    """)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert "NO-TRAP" not in r.stdout and r.returncode != 0, r.stdout + r.stderr[-400:]
 
 
 def test_nan_bytes_beyond_seq_len_do_not_leak(ops):
@@ -285,7 +324,7 @@ def test_nan_bytes_beyond_seq_len_do_not_leak(ops):
     torch.ops.b200attn.kv_write(c.d_key, c.d_value, c.kc, c.vc, c.d_slots, c.d_ks, c.d_vs)
     ws = ops.DecodeWorkspace("cuda", c.B, torch.uint8, num_ctas=2)
     out = torch.zeros(c.B, c.Hq, c.D, dtype=torch.bfloat16, device="cuda")
-    ws.make_plan(c.d_lens, c.Hq, c.Hkv)
+    ws.make_plan(c.d_lens, c.Hq, c.Hkv, c.d_bt, c.bs)
     ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale)
     torch.cuda.synchronize()
     assert_close(out.float().cpu().numpy(), c.oracle_decode(kc_o, vc_o), "fp8", "bf16")
@@ -296,7 +335,7 @@ def test_nan_bytes_beyond_seq_len_do_not_leak(ops):
     torch.ops.b200attn.kv_write(c2.d_key, c2.d_value, c2.kc, c2.vc, c2.d_slots, c2.d_ks, c2.d_vs)
     ws2 = ops.DecodeWorkspace("cuda", c2.B, torch.bfloat16, num_ctas=2)
     out2 = torch.zeros(c2.B, c2.Hq, c2.D, dtype=torch.bfloat16, device="cuda")
-    ws2.make_plan(c2.d_lens, c2.Hq, c2.Hkv)
+    ws2.make_plan(c2.d_lens, c2.Hq, c2.Hkv, c2.d_bt, c2.bs)
     ws2.decode(c2.d_q, c2.kc, c2.vc, c2.d_bt, c2.d_lens, out2, c2.d_ks, c2.d_vs, c2.sm_scale)
     torch.cuda.synchronize()
     assert_close(out2.float().cpu().numpy(), c2.oracle_decode(kc2, vc2), "bf16", "bf16")
@@ -374,7 +413,7 @@ def test_cuda_graph_capture_and_replay(ops):
     lens_buf = c.d_lens.clone()
 
     def step():
-        ws.make_plan(lens_buf, c.Hq, c.Hkv)
+        ws.make_plan(lens_buf, c.Hq, c.Hkv, c.d_bt, c.bs)
         ws.decode(c.d_q, c.kc, c.vc, c.d_bt, lens_buf, out, c.d_ks, c.d_vs, c.sm_scale)
 
     s = torch.cuda.Stream()

@@ -75,7 +75,7 @@ class Big:
     def decode(self, ctas=None, kc=None, vc=None, bt=None, q=None):
         ws = self.ops.DecodeWorkspace("cuda", self.B, self.dt, num_ctas=ctas)
         out = torch.full((self.B, self.Hq, D), float("nan"), dtype=torch.bfloat16, device="cuda")
-        ws.make_plan(self.d_lens, self.Hq, self.Hkv)
+        ws.make_plan(self.d_lens, self.Hq, self.Hkv, self.bt if bt is None else bt, BS)
         ws.decode(self.q if q is None else q, self.kc if kc is None else kc, self.vc if vc is None else vc,
                   self.bt if bt is None else bt, self.d_lens, out, self.ks, self.vs, self.sm_scale)
         torch.cuda.synchronize()

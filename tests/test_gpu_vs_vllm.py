@@ -83,7 +83,7 @@ def test_decode_vs_vllm_triton_unified_attention(vllm_ops, kv, tol, segs):
                       kv_quant_mode=KVQuantMode.FP8_PER_TENSOR if fp8 else KVQuantMode.NONE, **kw)
     ws = ops.DecodeWorkspace("cuda", B, torch.uint8 if fp8 else torch.bfloat16)
     out = torch.zeros(B, Hq, D, dtype=torch.bfloat16, device="cuda")
-    ws.make_plan(c.d_lens, Hq, Hkv)
+    ws.make_plan(c.d_lens, Hq, Hkv, c.d_bt, c.bs)
     ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale)
     torch.cuda.synchronize()
     got, want = out.float().cpu().numpy(), ref.float().cpu().numpy()

@@ -51,7 +51,7 @@ def decode(kc, vc, bt, ln, q, want_lse):
     ws = ops.DecodeWorkspace(dev, B, torch.uint8, group_size=q.shape[1])
     out = torch.zeros(B, q.shape[1], D, dtype=torch.bfloat16, device=dev)
     lse = torch.full((B, q.shape[1]), float("-inf"), dtype=torch.float32, device=dev) if want_lse else None
-    ws.make_plan(ln, q.shape[1], 1)
+    ws.make_plan(ln, q.shape[1], 1, bt, kc.shape[1])
     ws.decode(q, kc, vc, bt, ln, out, ks, vs, D ** -0.5, lse=lse)
     return out, lse
 
@@ -83,7 +83,7 @@ assert t.item() <= 1e-2, t.item()
 # ---- the same exchange over NVLink peer memory: decode writes its partial into a symmetric buffer, barrier, peer-load merge ----
 px = P.PeerExchange(B, Hg, D, torch.bfloat16, dev)
 ws = ops.DecodeWorkspace(dev, B, torch.uint8, group_size=Hg)
-ws.make_plan(ln, Hg, 1)
+ws.make_plan(ln, Hg, 1, bt, kc.shape[1])
 
 
 def layer():

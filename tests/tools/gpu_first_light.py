@@ -30,7 +30,7 @@ def run(name, lens, Hq, Hkv, kv, act="bf16", ctas=None, per_head=False, layout="
         ws = DecodeWorkspace("cuda", c.B, torch.uint8 if c.fp8 else torch.bfloat16, num_ctas=ctas)
         out = torch.full((c.B, Hq, c.D), float("nan"), dtype=c.d_q.dtype, device="cuda")
         lse = torch.zeros(c.B, Hq, dtype=torch.float32, device="cuda")
-        ws.make_plan(c.d_lens, Hq, Hkv)
+        ws.make_plan(c.d_lens, Hq, Hkv, c.d_bt, c.bs)
         ws.decode(c.d_q, c.kc, c.vc, c.d_bt, c.d_lens, out, c.d_ks, c.d_vs, c.sm_scale, lse)
         torch.cuda.synchronize()
         got = out.float().cpu().numpy()

@@ -53,7 +53,7 @@ def main():
         for dbg in [int(x) for x in a.debug.split(",")]:
             lib.b200attn_set_option(b"debug", dbg)
             ws = ops.DecodeWorkspace(dev, B, kv_t, num_ctas=ctas or None)
-            ws.make_plan(d_lens, Hq, Hkv)
+            ws.make_plan(d_lens, Hq, Hkv, bt, bs)
             torch.cuda.synchronize()
 
             def timed(fn):
@@ -68,8 +68,8 @@ def main():
                 t = np.array([x.elapsed_time(y) for x, y in evs]) * 1e3
                 return float(t.mean()), float(np.median(t)), float(t.min())
 
-            td = timed(lambda l: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.num_ctas))
-            tm = timed(lambda l: ops.launch_merge(caches[l][0], d_lens, out, ws.plan, ws.workspace, vs, ws.num_ctas))
+            td = timed(lambda l: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.grid))
+            tm = timed(lambda l: ops.launch_merge(caches[l][0], d_lens, out, ws.plan, ws.workspace, vs, ws.grid))
             tw = timed(lambda l: torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs))
             tall = timed(lambda l: (torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs), ws.decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ks, vs, D ** -0.5)))
             if a.graph:
@@ -90,15 +90,15 @@ def main():
                         g.replay()
                     e1.record(); torch.cuda.synchronize()
                     return e0.elapsed_time(e1) * 1e3 / iters / a.layers
-                dec = lambda l: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.num_ctas)
-                mrg = lambda l: ops.launch_merge(caches[l][0], d_lens, out, ws.plan, ws.workspace, vs, ws.num_ctas)
+                dec = lambda l: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.grid)
+                mrg = lambda l: ops.launch_merge(caches[l][0], d_lens, out, ws.plan, ws.workspace, vs, ws.grid)
                 wrt = lambda l: torch.ops.b200attn.kv_write(kn, vn, caches[l][0], caches[l][1], slots, ks, vs)
                 for pdl in (0, 1):
                     lib.b200attn_set_option(b"pdl", pdl)
                     t_d = graph_time(lambda: [dec(l) for l in range(a.layers)])
                     t_dm = graph_time(lambda: [(dec(l), mrg(l)) for l in range(a.layers)])
                     t_wdm = graph_time(lambda: [(wrt(l), dec(l), mrg(l)) for l in range(a.layers)])
-                    decf = lambda l, fr: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.num_ctas, None, None, fr, True)
+                    decf = lambda l, fr: ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, d_lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.grid, None, None, fr, True)
                     t_f = graph_time(lambda: [decf(l, -1) for l in range(a.layers)])
                     t_wf = graph_time(lambda: [(wrt(l), decf(l, -1)) for l in range(a.layers)])
                     t_wf1 = graph_time(lambda: [(wrt(l), decf(l, 1)) for l in range(a.layers)])
@@ -108,7 +108,7 @@ def main():
                     print(f"  graph/layer pdl={pdl}: decode {t_d:.2f} | decode+merge {t_dm:.2f} | write+decode+merge {t_wdm:.2f} | write only {t_w:.2f} | merge only {t_m:.2f} us"
                           f"  => decode {dec_b / t_d / 1e3:.0f} GB/s, all {(dec_b + wr_b) / t_wdm / 1e3:.0f} GB/s", flush=True)
                 lib.b200attn_set_option(b"pdl", a.pdl)
-            print(f"B={B} L={L} ({Hq},{Hkv}) {a.kv} tc={a.tc} ctas={ws.num_ctas} debug={dbg} pdl={a.pdl} | decode mean {td[0]:.2f} med {td[1]:.2f} min {td[2]:.2f} us "
+            print(f"B={B} L={L} ({Hq},{Hkv}) {a.kv} tc={a.tc} ctas={ws.grid} debug={dbg} pdl={a.pdl} | decode mean {td[0]:.2f} med {td[1]:.2f} min {td[2]:.2f} us "
                   f"= {dec_b / td[1] / 1e3:.0f} GB/s | merge {tm[1]:.2f} us | kv_write {tw[1]:.2f} us | write+decode+merge {tall[1]:.2f} us", flush=True)
     lib.b200attn_set_option(b"debug", 0)
 

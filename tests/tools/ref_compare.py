@@ -20,7 +20,7 @@ from tests.tools.workloads import WORKLOADS, Problem
 def time_ours(P, lib, pdl):
     w = P.w
     ws = ops.DecodeWorkspace(P.q.device, w["B"], P.kv_t, head_dim=w["D"], group_size=w["Hq"] // w["Hkv"])
-    ws.make_plan(P.lens, w["Hq"], w["Hkv"])
+    ws.make_plan(P.lens, w["Hq"], w["Hkv"], P.bt, w["bs"])
     torch.cuda.synchronize()
     lib.b200attn_set_option(b"pdl", pdl)
 

@@ -61,7 +61,7 @@ def main():
             out = torch.zeros(B, Hq, D, dtype=torch.bfloat16, device=dev)
             ks = torch.full((Hkv,), 0.01, device=dev); vs = torch.full((Hkv,), 0.01, device=dev)
             ws = ops.DecodeWorkspace(dev, B, kv_t, num_ctas=a.ctas or None, group_size=Hq // Hkv)
-            ws.make_plan(d_lens, Hq, Hkv)
+            ws.make_plan(d_lens, Hq, Hkv, bt, bs)
 
             def body():
                 for l in range(layers):

@@ -61,7 +61,7 @@ def time_us(body, iters=10):
 # ---- tp = 8: this rank holds every other run of 16 tokens: L / 2 tokens per sequence ----
 cs, bt, ln = caches(L // world)
 ws = ops.DecodeWorkspace(dev, B, torch.uint8, group_size=G)
-ws.make_plan(ln, G, 1)
+ws.make_plan(ln, G, 1, bt, cs[0][0].shape[1])
 px = P.PeerExchange(B, G, D, torch.bfloat16, dev)
 
 
@@ -84,7 +84,7 @@ torch.cuda.empty_cache()
 # ---- tp = 4: one rank, whole context, no exchange (every rank runs it; max over ranks) ----
 cs4, bt4, ln4 = caches(L)
 ws4 = ops.DecodeWorkspace(dev, B, torch.uint8, group_size=G)
-ws4.make_plan(ln4, G, 1)
+ws4.make_plan(ln4, G, 1, bt4, cs4[0][0].shape[1])
 out4 = torch.zeros(B, G, D, dtype=torch.bfloat16, device=dev)
 
 

@@ -13,8 +13,8 @@ lens = torch.full((B,), L, dtype=torch.int32, device=dev)
 caches = [torch.randint(0, 0x78, (nb, 2, Hkv, bs, D), dtype=torch.uint8, device=dev).permute(0, 1, 3, 2, 4).unbind(1) for _ in range(layers)]
 q = torch.randn(B, Hq, D, device=dev).to(torch.bfloat16); out = torch.zeros_like(q)
 ks = torch.full((Hkv,), 0.01, device=dev); vs = torch.full((Hkv,), 0.01, device=dev)
-ws = ops.DecodeWorkspace(dev, B, torch.uint8, num_ctas=int(os.environ.get("B200_CTAS", "0")) or None); ws.make_plan(lens, Hq, Hkv)
-buf = torch.zeros(ws.num_ctas * 8, dtype=torch.int64, device=dev)
+ws = ops.DecodeWorkspace(dev, B, torch.uint8, num_ctas=int(os.environ.get("B200_CTAS", "0")) or None); ws.make_plan(lens, Hq, Hkv, bt, bs)
+buf = torch.zeros(ws.grid * 8, dtype=torch.int64, device=dev)
 lib.b200attn_set_option(b"pdl", 0)
 lib.b200attn_set_option(b"tc", int(os.environ.get("B200_TC", "1")))
 fn = lib.b200attn_debug_set_timeline_buffer; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
@@ -22,7 +22,7 @@ for dbg in (0,):
     lib.b200attn_set_option(b"debug", dbg)
     for l in range(layers):
         fn(buf.data_ptr() if l == layers - 1 else None)
-        ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.num_ctas)
+        ops.launch_split_decode(q, caches[l][0], caches[l][1], bt, lens, out, ws.plan, ws.workspace, ks, vs, D ** -0.5, ws.grid)
     torch.cuda.synchronize()
     t = buf.cpu().numpy().reshape(-1, 8).astype(np.float64)
     act = t[:, 1] > 0
