@@ -1,21 +1,32 @@
 #!/usr/bin/env python
 """bench.py — paged decode-attention HBM GB/s and decode tok/s of the AR-stage hot path on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|thinker|...]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference|flashinfer|triton] [--workload c2|thinker|...]
 
 Workload (BASELINE.json configs[1], made concrete in SURVEY.md §8d "C2"): Qwen3-TTS talker streaming decode, FP8-e4m3
 KV cache, batch 64, 4k context, (Hq, Hkv, D) = (16, 2, 128), block size 16, 20 layers, synthetic data.
-One STEP = one decode step of the attention path of the whole model: the split-KV plan once, then for each of the
-20 layers the KV write of the new token (+FP8 quantisation), the split-KV paged decode kernel and the merge kernel.
+One STEP = one decode step of the attention path of the whole model, driven through the vLLM plugin classes exactly as
+the reference's runner drives them: `MetadataBuilder.build` once (eager: row buffers + the device-side split-KV plan),
+then for each of the 20 layers `Impl.do_kv_cache_update` (KV write + FP8 quantisation) and `Impl.forward` (split-KV paged
+decode with the merge in-kernel), the 40 layer launches replayed as one CUDA graph like vLLM's FULL cudagraph mode.
 All 20 per-layer caches (2.7 GB) are distinct, so every step streams far more than the 126 MB L2 (no flush needed).
 
-JSON keys (one line, rank 0): see the task contract.  `value` = algorithmic bytes of a step / device time with inputs
-resident in HBM (CUDA-graph replay); `e2e` = the same through the public ops with HOST inputs/outputs (pinned
-H2D of q/k/v/metadata and D2H of the attention output inside the timed region); `roofline` = the decode kernel alone,
-timed per launch with CUDA events; `cpu_baseline` = the C/OpenMP oracle port on the host cores (bounded sample).
-N > 1: KV heads are sharded across ranks (vLLM TP layout): every rank owns Hkv KV heads (and their G*Hkv query heads)
-of a model with N*Hkv KV heads, its own cache shard, replicated block tables — weak scaling, no data-path collective
-(vLLM's row-parallel o_proj consumes head-sharded outputs; the optional output all-gather is `--allgather`).
+JSON keys (one line, rank 0): see the task contract.
+  value     algorithmic bytes of a step / device time, inputs resident in HBM, K steps in one timed region (CUDA events);
+            `distribution` = median / p10 / p90 over >= 100 individually timed steps.
+  e2e       the same plugin calls with HOST inputs: pinned H2D of q/k/v/metadata and D2H of the attention output inside
+            the timed region, every step.
+  roofline  the decode kernel alone: one launch per layer cache, launched exactly as the step launches it (programmatic
+            dependent launch on), CUDA events around the graph replays; `isolated` = the same with PDL off (no overlap
+            between neighbouring launches).
+  vs_sm100_reference   the reference's own Blackwell kernels on the same inputs, same method (FlashInfer TRT-LLM-gen with
+            bf16 and fp8 query, Triton unified_attention, FA4 for bf16 KV, vLLM's reshape_and_cache_flash).
+  cpu_baseline   the C/OpenMP oracle port on the host cores (bounded sample).
+N > 1: `value` stays the weak-scaling line (every rank owns Hkv KV heads of a model with N*Hkv KV heads: vLLM's TP layout,
+no data-path collective); `sharded` adds the north-star config: the Qwen3-Omni thinker (Hq 32 / Hkv 4, B 32, 32k, fp8)
+STRONG-scaled over the N GPUs -- by KV head up to 4, KV head x 2-way sequence split through NVLink peer memory at 8.
+--impl reference: the oracle's C/OpenMP port on the host cores (the reference's CPU backend is not in this wheel);
+--impl flashinfer / triton: the reference's GPU kernels through the same step (comparison arms, never the product).
 """
 from __future__ import annotations
 
@@ -27,30 +38,17 @@ import subprocess
 import sys
 import threading
 import time
+import types
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+_FI = os.path.join(ROOT, "baseline", "_fi")
+if os.path.isdir(_FI):   # FlashInfer's JIT cache prebuilt in-tree (baseline/_fi, git-ignored): no 80 s compile on the box
+    os.environ.setdefault("FLASHINFER_WORKSPACE_BASE", _FI)
 
-WORKLOADS = {
-    # name: (B, L, Hq, Hkv, D, block_size, kv, layers, description)
-    "c2": dict(B=64, L=4096, Hq=16, Hkv=2, D=128, bs=16, kv="fp8", layers=20,
-               desc="Qwen3-TTS talker streaming decode, FP8 KV, batch 64, 4k context (BASELINE configs[1])"),
-    "c2-bf16": dict(B=64, L=4096, Hq=16, Hkv=2, D=128, bs=16, kv="bf16", layers=20, desc="C2 with bf16 KV"),
-    "thinker": dict(B=32, L=32768, Hq=32, Hkv=4, D=128, bs=16, kv="fp8", layers=2,
-                    desc="Qwen3-Omni thinker decode, FP8 KV, 32k context (BASELINE configs[3], 2 layers resident)"),
-    "c1": dict(B=1, L=2048, Hq=16, Hkv=2, D=128, bs=16, kv="bf16", layers=20, desc="talker B1 2k bf16 (configs[0])"),
-}
-
-
-def algorithmic_bytes(lens, Hq, Hkv, D, bs, s_kv):
-    """BASELINE.md 'Algorithmic bytes': (decode bytes, kv-write bytes) per layer call."""
-    lens = np.asarray(lens, dtype=np.int64)
-    B = len(lens)
-    dec = int((2 * lens * Hkv * D * s_kv).sum() + 2 * B * Hq * D * 2 + (-(-lens // bs) * 4).sum() + 4 * B)
-    wr = int(B * Hkv * D * (2 * 2 + 2 * s_kv) + 8 * B)
-    return dec, wr
+from tests.tools.workloads import WORKLOADS, algorithmic_bytes, seq_lens_of  # noqa: E402
 
 
 def load_peaks():
@@ -62,7 +60,7 @@ def load_peaks():
 
 
 # ------------------------------------------------------------------------------------------------
-# clocks sampler (nvidia-smi during the timed region)
+# clocks sampler (NVML during the timed region)
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
     """Polls NVML (pynvml) every 2 ms from a thread while `active`; falls back to `nvidia-smi -lms 20` when NVML is missing."""
@@ -70,7 +68,7 @@ class ClockSampler:
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.samples = []   # (sm_mhz, sm_max_mhz, reasons bitmask)
+        self.samples = []   # (sm_mhz, sm_max_mhz, reasons)
         self.active = False
         self._stop = False
         self._thread = None
@@ -80,9 +78,8 @@ class ClockSampler:
         try:
             import pynvml
             pynvml.nvmlInit()
-            # honour CUDA_VISIBLE_DEVICES: map the CUDA ordinal to the NVML device through its UUID
             import torch
-            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)   # honour CUDA_VISIBLE_DEVICES
             try:
                 h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
             except Exception:  # noqa: BLE001
@@ -147,8 +144,8 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle's C/OpenMP port on the host cores (cpu_baseline, and --impl reference)
 # ------------------------------------------------------------------------------------------------
-def cpu_oracle_layer(w, reps_budget_s=15.0, max_reps=5, seed=0):
-    """Time one layer (KV write + paged decode) of workload `w` on the CPU.  Returns (seconds per layer, cores, sample)."""
+def cpu_oracle_layer(w, reps_budget_s=15.0, max_reps=5, seed=0, warmup=1):
+    """Time one layer (KV write + paged decode) of workload `w` on the CPU.  Returns (times, cores, sample)."""
     path = os.path.join(ROOT, "oracle", "liboracle.so")
     if not os.path.exists(path):
         subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
@@ -158,13 +155,18 @@ def cpu_oracle_layer(w, reps_budget_s=15.0, max_reps=5, seed=0):
     except Exception:  # noqa: BLE001
         pass
     cores = int(lib.oracle_num_threads())
-    B, L, Hq, Hkv, D, bs = w["B"], w["L"], w["Hq"], w["Hkv"], w["D"], w["bs"]
+    B, Hq, Hkv, D, bs = w["B"], w["Hq"], w["Hkv"], w["D"], w["bs"]
+    lens = seq_lens_of(w)
     fp8 = w["kv"] == "fp8"
     rng = np.random.default_rng(seed)
-    nblk_seq = -(-L // bs)
-    nb = B * nblk_seq + 1
-    bt = rng.permutation(nb - 1)[: B * nblk_seq].reshape(B, nblk_seq).astype(np.int32)
-    lens = np.full(B, L, dtype=np.int32)
+    nblk = -(-lens.astype(np.int64) // bs)
+    nb = int(nblk.sum()) + 1
+    perm = rng.permutation(nb - 1).astype(np.int32)
+    bt = np.zeros((B, int(nblk.max())), np.int32)
+    off = 0
+    for s in range(B):
+        bt[s, : nblk[s]] = perm[off: off + nblk[s]]
+        off += int(nblk[s])
     if fp8:   # NaN-free random e4m3 bytes (|x| <= 240)
         kc = (rng.integers(0, 0x78, size=(nb, bs, Hkv, D), dtype=np.uint8) | (rng.integers(0, 2, size=(nb, bs, Hkv, D), dtype=np.uint8) << 7))
         vc = (rng.integers(0, 0x78, size=(nb, bs, Hkv, D), dtype=np.uint8) | (rng.integers(0, 2, size=(nb, bs, Hkv, D), dtype=np.uint8) << 7))
@@ -174,7 +176,8 @@ def cpu_oracle_layer(w, reps_budget_s=15.0, max_reps=5, seed=0):
     bf = lambda a: (a.astype(np.float32).view(np.uint32) >> 16).astype(np.uint16)  # noqa: E731
     q = bf(rng.standard_normal((B, Hq, D)))
     kn, vn = bf(rng.standard_normal((B, Hkv, D))), bf(rng.standard_normal((B, Hkv, D)))
-    slots = (bt[:, (L - 1) // bs].astype(np.int64) * bs + (L - 1) % bs)
+    last = lens.astype(np.int64) - 1
+    slots = bt[np.arange(B), last // bs].astype(np.int64) * bs + last % bs
     ks = np.full(Hkv, 0.01, np.float32); vs = np.full(Hkv, 0.01, np.float32)
     out = np.zeros((B, Hq, D), np.float32)
     p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
@@ -184,39 +187,15 @@ def cpu_oracle_layer(w, reps_budget_s=15.0, max_reps=5, seed=0):
         lib.oracle_paged_decode(p(q), p(kc), p(vc), p(bt), C.c_int64(bt.shape[1]), p(lens), B, Hq, Hkv, D, bs, 0, int(fp8),
                                 C.c_float(D ** -0.5), p(ks), p(vs), 1, p(out))
 
-    once()  # warm-up (page-in)
+    for _ in range(max(1, warmup)):
+        once()  # warm-up (page-in)
     times = []
     t_start = time.perf_counter()
     while len(times) < max_reps and (time.perf_counter() - t_start) < reps_budget_s:
         t0 = time.perf_counter(); once(); times.append(time.perf_counter() - t0)
-    sample = f"1 of {w['layers']} layers (KV write + paged decode, B={B}, L={L}), {len(times)} reps after 1 warm-up, median"
+    sample = (f"1 of {w['layers']} layers (KV write + paged decode, B={B}, ctx={w['L']}), {len(times)} reps after "
+              f"{max(1, warmup)} warm-up, median")
     return times, cores, sample
-
-
-def run_reference(args, w):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    s_kv = 1 if w["kv"] == "fp8" else 2
-    dec_b, wr_b = algorithmic_bytes([w["L"]] * w["B"], w["Hq"], w["Hkv"], w["D"], w["bs"], s_kv)
-    # a reference "step" is a bounded sample: ONE layer of the step on the host cores (1 untimed warm-up inside)
-    times, cores, _ = cpu_oracle_layer(w, reps_budget_s=120.0, max_reps=max(1, min(args.steps, 5)))
-    t = float(np.median(times))
-    gbs = (dec_b + wr_b) / t / 1e9
-    sample = f"step = 1 of {w['layers']} layers on the host (oracle/oracle.c, OpenMP), {len(times)} steps, median"
-    line = {
-        "impl": "reference", "metric": "paged_decode_attn_hbm_gbs", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
-        "steps": len(times), "warmup": 1, "ms_per_step": t * 1e3 * w["layers"], "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "fp32 (bf16 activations, e4m3 KV)" if w["kv"] == "fp8" else "fp32 (bf16)",
-        "data": "synthetic",
-        "config": workload_config(args, w, 0),
-        "tok_s": w["B"] / (t * w["layers"]),
-        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "reference CPU backend (vLLM cpu_attn) is not compiled into the CUDA wheel in this image; this arm times the "
-                "oracle's C/OpenMP port of the reference algorithm on all host cores; ms_per_step is extrapolated to all layers",
-    }
-    emit(json.dumps(line))
 
 
 def workload_config(args, w, num_ctas):
@@ -227,6 +206,150 @@ def workload_config(args, w, num_ctas):
             "allgather": args.allgather}
 
 
+def run_reference(args, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    s_kv = 1 if w["kv"] == "fp8" else 2
+    dec_b, wr_b = algorithmic_bytes(seq_lens_of(w), w["Hq"], w["Hkv"], w["D"], w["bs"], s_kv)
+    # a reference "step" is a bounded sample of the step: ONE of its layers on the host cores; --steps / --warmup are honoured
+    times, cores, _ = cpu_oracle_layer(w, reps_budget_s=240.0, max_reps=max(1, args.steps), warmup=max(1, args.warmup))
+    t = float(np.median(times))
+    gbs = (dec_b + wr_b) / t / 1e9
+    sample = f"step = 1 of {w['layers']} layers on the host (oracle/oracle.c, OpenMP), {len(times)} steps, median"
+    line = {
+        "impl": "reference", "metric": "paged_decode_attn_hbm_gbs", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": len(times), "warmup": max(1, args.warmup), "ms_per_step": t * 1e3 * w["layers"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "fp32 (bf16 activations, e4m3 KV)" if w["kv"] == "fp8" else "fp32 (bf16)", "data": "synthetic",
+        "config": workload_config(args, w, 0),
+        "tok_s": w["B"] / (t * w["layers"]),
+        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference CPU backend (vLLM cpu_attn) is not compiled into the CUDA wheel in this image; this arm times the "
+                "oracle's C/OpenMP port of the reference algorithm on all host cores; ms_per_step is extrapolated to all layers",
+    }
+    emit(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+# helpers shared by the GPU arms
+# ------------------------------------------------------------------------------------------------
+def capture(body, side):
+    """Warm `body` up on a side stream and capture it into a CUDA graph; returns (callable, captured?)."""
+    import torch
+
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        body(); body()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    try:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            body()
+        return g.replay, True
+    except Exception as e:  # noqa: BLE001
+        print(f"# graph capture failed ({type(e).__name__}: {str(e)[:200]}); timing eager launches", file=sys.stderr)
+        torch.cuda.synchronize()
+        return body, False
+
+
+def time_region(run, n, barrier):
+    import torch
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(n):
+        run()
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1)
+
+
+def max_over_ranks(ms, dev, world):
+    if world <= 1:
+        return ms
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+class PluginStep:
+    """The hot path as vLLM drives it: B200PagedAttentionMetadataBuilder.build -> per layer Impl.do_kv_cache_update +
+    Impl.forward ($VLLM/model_executor/layers/attention/attention.py:437-529; caller
+    vllm_omni/worker/gpu_ar_model_runner.py:228-298).  Config objects are stand-ins with the fields the classes read."""
+
+    def __init__(self, P, dev):
+        import torch
+        from vllm.v1.attention.backend import CommonAttentionMetadata
+
+        from ht_vllm_omni_b200 import backend as BK
+
+        w = P.w
+        B, Hq, Hkv, D, bs = w["B"], w["Hq"], w["Hkv"], w["D"], w["bs"]
+        self.P, self.B, self.Hq, self.Hkv, self.D = P, B, Hq, Hkv, D
+        be = BK.B200PagedAttentionBackend
+        self.impl = be.get_impl_cls()(Hq, D, P.sm_scale, Hkv, None, None, "fp8" if P.fp8 else "auto")
+        self.layer = types.SimpleNamespace(_k_scale=P.k_scale, _v_scale=P.v_scale, _k_scale_float=1.0, _v_scale_float=1.0)
+        mc = types.SimpleNamespace(get_num_attention_heads=lambda pc: Hq, get_num_kv_heads=lambda pc: Hkv, get_head_size=lambda: D)
+        cfg = types.SimpleNamespace(model_config=mc, parallel_config=None, scheduler_config=types.SimpleNamespace(max_num_batched_tokens=B))
+        self.builder = be.get_builder_cls()(types.SimpleNamespace(block_size=bs, dtype=P.kv_t), [f"l{i}" for i in range(P.NL)], cfg, dev)
+        self.kv_caches = [ph.permute(0, 1, 3, 2, 4) for ph in P.phys]   # logical [nb, 2, bs, Hkv, D] over HND memory (vLLM's view)
+        qsl = torch.arange(B + 1, dtype=torch.int32)
+        self.cm = CommonAttentionMetadata(query_start_loc=qsl.to(dev), query_start_loc_cpu=qsl, seq_lens=P.lens, num_reqs=B,
+                                          num_actual_tokens=B, max_query_len=1, max_seq_len=int(P.lens_np.max()),
+                                          block_table_tensor=P.bt, slot_mapping=P.step_slots)
+        self.md = self.builder.build(0, self.cm)
+        self.q2 = P.q.view(P.NL, B, Hq * D); self.k2 = P.kn.view(P.NL, B, Hkv * D); self.v2 = P.vn.view(P.NL, B, Hkv * D)
+        self.o2 = P.out.view(P.NL, B, Hq * D)
+
+    def build(self):
+        self.md = self.builder.build(0, self.cm)   # eager, before every step / replay -- as vLLM does
+
+    def layers(self, lo=0, hi=None):
+        for l in range(lo, self.P.NL if hi is None else hi):
+            self.impl.do_kv_cache_update(self.layer, self.k2[l], self.v2[l], self.kv_caches[l], self.cm.slot_mapping)
+            self.impl.forward(self.layer, self.q2[l], self.k2[l], self.v2[l], self.kv_caches[l], self.md, self.o2[l])
+
+    @property
+    def grid(self):
+        return self.builder.workspace.grid
+
+
+class OpsStep:
+    """Fallback when the vLLM plugin classes cannot be imported on the box: the same launches through torch.ops.b200attn.*."""
+
+    def __init__(self, P, dev):
+        import ht_vllm_omni_b200.ops as ops
+
+        w = P.w
+        self.P = P
+        self.ws = ops.DecodeWorkspace(dev, w["B"], P.kv_t, head_dim=w["D"], group_size=w["Hq"] // w["Hkv"])
+        self.build()
+
+    def build(self):
+        w = self.P.w
+        self.ws.make_plan(self.P.lens, w["Hq"], w["Hkv"], self.P.bt, w["bs"])
+
+    def layers(self, lo=0, hi=None):
+        import torch
+
+        P = self.P
+        for l in range(lo, P.NL if hi is None else hi):
+            kc, vc = P.planes[l]
+            torch.ops.b200attn.kv_write(P.kn[l], P.vn[l], kc, vc, P.step_slots, P.k_scale, P.v_scale)
+            self.ws.decode(P.q[l], kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale, P.sm_scale, fresh_tokens=1)
+
+    @property
+    def grid(self):
+        return self.ws.grid
+
+
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
@@ -235,7 +358,7 @@ def run_ours(args, w):
     import torch.distributed as dist
 
     import ht_vllm_omni_b200.ops as ops
-    from ht_vllm_omni_b200.ops import DecodeWorkspace
+    from tests.tools.workloads import Problem
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -246,75 +369,30 @@ def run_ours(args, w):
         dist.init_process_group("nccl", device_id=dev)
     lib = ops.load_library()
 
-    B, L, Hq, Hkv, D, bs, NL = w["B"], w["L"], w["Hq"], w["Hkv"], w["D"], w["bs"], w["layers"]
-    fp8 = w["kv"] == "fp8"
-    s_kv = 1 if fp8 else 2
-    kv_t = torch.uint8 if fp8 else torch.bfloat16
-    lens_np = np.full(B, L, dtype=np.int32)
-    g = torch.Generator(device=dev).manual_seed(1234 + rank)
-    # ---- per-layer paged caches (HND physical), filled THROUGH the write path from N(0,1) tokens ----
-    nblk_seq = -(-L // bs)
-    nb = int(B * nblk_seq * 1.1) + 1
-    perm = torch.randperm(nb, generator=torch.Generator().manual_seed(99))[: B * nblk_seq].to(torch.int32)
-    bt = perm.reshape(B, nblk_seq).contiguous()
-    pos = torch.arange(L, dtype=torch.int64)
-    slots_all = (bt.to(torch.int64)[:, pos // bs] * bs + (pos % bs)[None, :]).reshape(-1).to(dev)
-    d_bt, d_lens = bt.to(dev), torch.from_numpy(lens_np).to(dev)
-    k_scale = torch.full((Hkv,), 4.5 / 448.0, dtype=torch.float32, device=dev)   # N(0,1) tokens: |x| <= 4.5 sigma
-    v_scale = torch.full((Hkv,), 4.5 / 448.0, dtype=torch.float32, device=dev)
-    caches = []
-    for _ in range(NL):
-        phys = torch.zeros((nb, 2, Hkv, bs, D), dtype=kv_t, device=dev)
-        kc, vc = phys.permute(0, 1, 3, 2, 4).unbind(1)
-        chunk = 1 << 16
-        for s0 in range(0, B * L, chunk):
-            n = min(chunk, B * L - s0)
-            kk = torch.randn(n, Hkv, D, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
-            vv = torch.randn(n, Hkv, D, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
-            torch.ops.b200attn.kv_write(kk, vv, kc, vc, slots_all[s0:s0 + n], k_scale, v_scale)
-        caches.append((kc, vc))
-    torch.cuda.synchronize()
-    # ---- per-step device inputs/outputs (the graph reads these fixed buffers) ----
-    q = torch.randn(NL, B, Hq, D, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
-    kn = torch.randn(NL, B, Hkv, D, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
-    vn = torch.randn(NL, B, Hkv, D, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
-    out = torch.zeros(NL, B, Hq, D, dtype=torch.bfloat16, device=dev)
-    step_slots = (bt.to(torch.int64)[:, (L - 1) // bs] * bs + (L - 1) % bs).to(dev)   # the newest token of each sequence
-    ws = DecodeWorkspace(dev, B, kv_t, head_dim=D, num_ctas=args.ctas or None)
+    B, Hq, Hkv, D, bs, NL = w["B"], w["Hq"], w["Hkv"], w["D"], w["bs"], w["layers"]
+    P = Problem(w, dev, seed=1234 + rank, fill="write")   # caches filled THROUGH the write path from N(0,1) tokens
+    try:
+        S = PluginStep(P, dev)
+        api = "vLLM plugin classes: B200PagedAttentionMetadataBuilder.build + Impl.do_kv_cache_update + Impl.forward per layer"
+    except Exception as e:  # noqa: BLE001
+        print(f"# vLLM plugin classes unavailable ({type(e).__name__}: {str(e)[:200]}); driving torch.ops.b200attn directly", file=sys.stderr)
+        S = OpsStep(P, dev)
+        api = "torch.ops.b200attn.* (vLLM not importable on this box)"
     gathered = torch.empty(world, NL, B, Hq, D, dtype=torch.bfloat16, device=dev) if (world > 1 and args.allgather != "none") else None
-    sm_scale = D ** -0.5
+
+    def hooks():
+        S.layers()
+        if gathered is not None:
+            dist.all_gather_into_tensor(gathered, P.out)
+
+    side = torch.cuda.Stream(device=dev)
+    replay, use_graph = (hooks, False) if args.no_graph else capture(hooks, side)
 
     def step():
-        ws.make_plan(d_lens, Hq, Hkv, d_bt, bs)
-        for l in range(NL):
-            kc, vc = caches[l]
-            torch.ops.b200attn.kv_write(kn[l], vn[l], kc, vc, step_slots, k_scale, v_scale)
-            # fresh_tokens=1: a decode step's KV write touched only the newest position of each row (what backend.py passes)
-            ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale, fresh_tokens=1)
-        if gathered is not None:
-            dist.all_gather_into_tensor(gathered, out)
+        S.build()
+        replay()
 
     launches_per_step = 1 + 2 * NL   # plan + per layer: kv_write, decode (split-KV partials merged in-kernel)
-
-    # ---- capture one step into a CUDA graph ----
-    side = torch.cuda.Stream(device=dev)
-    side.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(side):
-        step(); step()
-    torch.cuda.current_stream().wait_stream(side)
-    torch.cuda.synchronize()
-    graph = torch.cuda.CUDAGraph()
-    use_graph = not args.no_graph
-    if use_graph:
-        try:
-            with torch.cuda.graph(graph):
-                step()
-        except Exception as e:  # noqa: BLE001
-            if rank == 0:
-                print(f"# graph capture failed ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
-            use_graph = False
-            torch.cuda.synchronize()
-    run_step = graph.replay if use_graph else step
 
     def barrier():
         if world > 1:
@@ -324,151 +402,138 @@ def run_ours(args, w):
     sampler = ClockSampler(local)
     sampler.start()
 
-    # ---- (1) device-resident timing ----
+    # ---- (1) device-resident timing: K steps in one region ----
     for _ in range(args.warmup):
-        run_step()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        step()
     sampler.active = True
-    e0.record()
-    for _ in range(args.steps):
-        run_step()
-    e1.record()
-    barrier()
+    ms = max_over_ranks(time_region(step, args.steps, barrier), dev, world)
     sampler.active = False
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
     ms_per_step = ms / args.steps
+    # distribution over >= 100 individually timed steps (20 warm-up + 100 timed, median and p10 / p90)
+    n_dist = max(100, args.steps)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_dist)]
+    barrier()
+    for a, b in evs:
+        a.record(); step(); b.record()
+    barrier()
+    per = np.array([a.elapsed_time(b) for a, b in evs])
+    dist_ms = {"steps": n_dist, "median_ms": float(np.median(per)), "p10_ms": float(np.percentile(per, 10)),
+               "p90_ms": float(np.percentile(per, 90)), "note": "each step bracketed by its own CUDA events (serialises host enqueue and device)"}
 
-    # ---- (2) end-to-end: host inputs -> pinned H2D -> step -> D2H of the attention output ----
-    h_q, h_kn, h_vn = q.cpu().pin_memory(), kn.cpu().pin_memory(), vn.cpu().pin_memory()
-    h_slots, h_lens, h_bt = step_slots.cpu().pin_memory(), d_lens.cpu().pin_memory(), d_bt.cpu().pin_memory()
-    h_out = torch.empty(out.shape, dtype=out.dtype).pin_memory()
+    # ---- (2) end-to-end: host inputs -> pinned H2D -> build + layer hooks -> D2H of the attention output, every step ----
+    h_q, h_kn, h_vn = P.q.cpu().pin_memory(), P.kn.cpu().pin_memory(), P.vn.cpu().pin_memory()
+    h_slots, h_lens, h_bt = P.step_slots.cpu().pin_memory(), P.lens.cpu().pin_memory(), P.bt.cpu().pin_memory()
+    h_out = torch.empty(P.out.shape, dtype=P.out.dtype).pin_memory()
     h2d_bytes = sum(t.numel() * t.element_size() for t in (h_q, h_kn, h_vn, h_slots, h_lens, h_bt))
     d2h_bytes = h_out.numel() * h_out.element_size()
-
-    # The host-buffer call is pipelined in layer groups: group g's inputs travel H2D on a copy stream while group g-1
-    # computes, and its outputs travel D2H on a second copy stream while group g+1 computes (PCIe is full duplex).  The
-    # whole step -- copies, plan, 2 x NL kernels -- is one CUDA graph with three stream branches.
+    # The layer part is pipelined in layer groups: group g's q/k/v travel H2D on a copy stream while group g-1 computes, and
+    # its outputs travel D2H on a second copy stream while group g+1 computes (PCIe is full duplex); the whole call is one
+    # CUDA graph with three stream branches.
     NG = int(os.environ.get("B200_E2E_GROUPS", "5"))
     NG = NG if (NG > 0 and NL % NG == 0) else 1
     GL = NL // NG
     s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
 
     def e2e_body():
+        # step metadata first (build() reads it), then build() -- capture-safe: two small copies + the device-side plan -- then
+        # the layer groups
+        P.step_slots.copy_(h_slots, non_blocking=True); P.lens.copy_(h_lens, non_blocking=True); P.bt.copy_(h_bt, non_blocking=True)
+        S.build()
         main = torch.cuda.current_stream()
         s_in.wait_stream(main)
         s_out.wait_stream(main)
         ev_in = []
         with torch.cuda.stream(s_in):
-            step_slots.copy_(h_slots, non_blocking=True); d_lens.copy_(h_lens, non_blocking=True); d_bt.copy_(h_bt, non_blocking=True)
             for gi in range(NG):
                 sl = slice(gi * GL, (gi + 1) * GL)
-                q[sl].copy_(h_q[sl], non_blocking=True); kn[sl].copy_(h_kn[sl], non_blocking=True); vn[sl].copy_(h_vn[sl], non_blocking=True)
+                P.q[sl].copy_(h_q[sl], non_blocking=True); P.kn[sl].copy_(h_kn[sl], non_blocking=True); P.vn[sl].copy_(h_vn[sl], non_blocking=True)
                 ev = torch.cuda.Event(); ev.record(s_in); ev_in.append(ev)
         for gi in range(NG):
             main.wait_event(ev_in[gi])
-            if gi == 0:
-                ws.make_plan(d_lens, Hq, Hkv, d_bt, bs)
-            for l in range(gi * GL, (gi + 1) * GL):
-                kc, vc = caches[l]
-                torch.ops.b200attn.kv_write(kn[l], vn[l], kc, vc, step_slots, k_scale, v_scale)
-                ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale, fresh_tokens=1)
+            S.layers(gi * GL, (gi + 1) * GL)
             ev = torch.cuda.Event(); ev.record(main)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev)
                 sl = slice(gi * GL, (gi + 1) * GL)
-                h_out[sl].copy_(out[sl], non_blocking=True)
+                h_out[sl].copy_(P.out[sl], non_blocking=True)
         main.wait_stream(s_in)
         main.wait_stream(s_out)
 
-    e2e_graph = None
+    e2e_replay, e2e_graphed = (e2e_body, False)
     if use_graph and gathered is None:
-        try:
-            with torch.cuda.stream(side):
-                e2e_body()
-            torch.cuda.synchronize()
-            e2e_graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(e2e_graph):
-                e2e_body()
-        except Exception as e:  # noqa: BLE001
-            if rank == 0:
-                print(f"# e2e graph capture failed ({type(e).__name__}: {e}); using the serial copy/step/copy path", file=sys.stderr)
-            e2e_graph = None
-            torch.cuda.synchronize()
+        e2e_replay, e2e_graphed = capture(e2e_body, side)
 
     def e2e_step():
-        if e2e_graph is not None:
-            e2e_graph.replay()
-        else:
-            q.copy_(h_q, non_blocking=True); kn.copy_(h_kn, non_blocking=True); vn.copy_(h_vn, non_blocking=True)
-            step_slots.copy_(h_slots, non_blocking=True); d_lens.copy_(h_lens, non_blocking=True); d_bt.copy_(h_bt, non_blocking=True)
-            run_step()
-            h_out.copy_(out, non_blocking=True)
+        e2e_replay()
         torch.cuda.current_stream().synchronize()   # the caller consumes the result every step
 
     for _ in range(max(3, args.warmup)):
         e2e_step()
-    barrier()
-    e0.record()
-    for _ in range(args.steps):
-        e2e_step()
-    e1.record()
-    barrier()
-    ms_e2e = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms_e2e], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_e2e = float(t.item())
+    ms_e2e = max_over_ranks(time_region(e2e_step, args.steps, barrier), dev, world)
     ms_e2e_per_step = ms_e2e / args.steps
 
-    # ---- (3) roofline leg: the decode kernel alone (split-KV + in-kernel merge, exactly the launch the step makes), NL launches
-    # over the NL distinct layer caches captured as one CUDA graph with PDL off (no overlap between neighbours), CUDA events
-    # around the replays on the launching stream; duration per launch = elapsed / launches ----
-    lib.b200attn_set_option(b"pdl", 0)
-    ws.make_plan(d_lens, Hq, Hkv, d_bt, bs)
+    # ---- (3) roofline leg: the decode kernel alone, NL launches over the NL distinct layer caches, one CUDA graph ----
+    ws = ops.DecodeWorkspace(dev, B, P.kv_t, head_dim=D, group_size=Hq // Hkv)
+    ws.make_plan(P.lens, Hq, Hkv, P.bt, bs)
     torch.cuda.synchronize()
 
     def decode_only():
         for l in range(NL):
-            kc, vc = caches[l]
-            ws.decode(q[l], kc, vc, d_bt, d_lens, out[l], k_scale, v_scale, sm_scale)
+            kc, vc = P.planes[l]
+            ws.decode(P.q[l], kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale, P.sm_scale, fresh_tokens=1)
 
-    reps = max(1, min(args.steps, 10))
-    kgraph = torch.cuda.CUDAGraph()
-    try:
-        with torch.cuda.stream(side):
-            decode_only()
-        torch.cuda.synchronize()
-        with torch.cuda.graph(kgraph):
-            decode_only()
-        run_k = kgraph.replay
-    except Exception:  # noqa: BLE001
-        torch.cuda.synchronize()
-        run_k = decode_only
-    for _ in range(2):
-        run_k()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(reps):
-        run_k()
-    b.record()
-    torch.cuda.synchronize()
+    reps = max(3, min(args.steps, 20))
+    kern = {}
+    for pdl in (1, 0):
+        lib.b200attn_set_option(b"pdl", pdl)
+        run_k, _ = capture(decode_only, side)
+        for _ in range(3):
+            run_k()
+        kern[pdl] = time_region(run_k, reps, lambda: torch.cuda.synchronize()) / (reps * NL)   # ms per launch
     lib.b200attn_set_option(b"pdl", 1)
-    evs = [None] * (reps * NL)
-    kern_ms = a.elapsed_time(b) / (reps * NL)
     sampler.stop()
+    ours_out = P.out.clone()
 
-    dec_b, wr_b = algorithmic_bytes(lens_np, Hq, Hkv, D, bs, s_kv)
+    dec_b, wr_b = P.dec_bytes, P.wr_bytes
     step_bytes = (dec_b + wr_b) * NL
     peak, peak_src = load_peaks()
     gbs = world * step_bytes / (ms_per_step * 1e-3) / 1e9
     gbs_e2e = world * step_bytes / (ms_e2e_per_step * 1e-3) / 1e9
-    kern_gbs = dec_b / (kern_ms * 1e-3) / 1e9
+    kern_gbs = dec_b / (kern[1] * 1e-3) / 1e9
+    kern_iso_gbs = dec_b / (kern[0] * 1e-3) / 1e9
+    fp8 = P.fp8
+    tc = fp8 and Hq // Hkv <= 8
+
+    # ---- (4) the reference's own sm_100 kernels on the same inputs (N = 1, rank 0) ----
+    sm100 = None
+    if world == 1 and not args.no_sm100_ref:
+        try:
+            from tests.tools import sm100_reference as R
+
+            arms = R.compare_all(P.phys, P.q, P.bt, P.lens, P.sm_scale, P.k_scale, P.v_scale, dec_b, wr_b, kn=P.kn, vn=P.vn,
+                                 slots=P.step_slots, ours_out=ours_out)
+            sm100 = {"method": "every arm: CUDA graph of one launch per layer cache, CUDA events, each library's default launch attributes "
+                               "(FlashInfer enables programmatic dependent launch on sm_100 by itself; so does our step); ratio_vs_ours = arm "
+                               "time / our time (`ours_us`, PDL on), > 1 means ours is faster", "ours_us": kern[1] * 1e3,
+                     "ours_isolated_pdl_off_us": kern[0] * 1e3}
+            for k, v in arms.items():
+                if "us_per_layer" in v and not k.startswith("vllm_reshape"):
+                    v["ratio_vs_ours"] = v["us_per_layer"] / (kern[1] * 1e3)
+                sm100[k] = v
+        except Exception as e:  # noqa: BLE001
+            sm100 = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+
+    # ---- (5) N > 1: the north-star sharded config, strong-scaled ----
+    sharded = None
+    if world > 1 and not args.no_sharded:
+        try:
+            from tests.tools.sharded_thinker import run_sharded
+
+            del P.phys, P.planes
+            torch.cuda.empty_cache()
+            sharded = run_sharded(dev, rank, world, lib)
+        except Exception as e:  # noqa: BLE001
+            sharded = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
 
     if world > 1:
         # every rank is past its last collective: leave without tearing NCCL down (communicators referenced by a captured
@@ -486,36 +551,92 @@ def run_ours(args, w):
         cpu = {"value": (dec_b + wr_b) / t_cpu / 1e9, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample,
                "tok_s": B / (t_cpu * NL)}
 
+    kname = ("b200attn::decode_tc_kernel" if tc else "b200attn::decode_kernel")
     line = {
         "metric": "paged_decode_attn_hbm_gbs", "value": gbs, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "fp8_e4m3 KV / bf16 Q,O / tcgen05 kind::f8f6f4 (exact hi+lo e4m3 split of Q and P), fp32 accumulate" if (fp8 and Hq // Hkv <= 8) else
+        "dtype": "fp8_e4m3 KV / bf16 Q,O / tcgen05 kind::f8f6f4 (exact hi+lo e4m3 split of Q and P), fp32 accumulate" if tc else
                  "fp8_e4m3 KV / bf16 Q,O / f16 HMMA, fp32 accumulate" if fp8 else "bf16 KV,Q,O / bf16 HMMA, fp32 accumulate",
         "data": "synthetic (N(0,1) tokens written through the KV-write path; random block permutation)",
-        "config": workload_config(args, w, ws.grid),
+        "config": workload_config(args, w, S.grid),
+        "api": api,
         "tok_s": B / (ms_per_step * 1e-3),
         "pct_of_8tbs": gbs / world / 8000.0 * 100.0, "pct_of_measured_hbm": gbs / world / peak * 100.0,
         "cuda_graph": use_graph,
+        "distribution": dist_ms,
         "e2e": {"value": gbs_e2e, "unit": "GB/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3),
-                "pipeline": f"one CUDA graph, {NG} layer groups: H2D / compute / D2H on three stream branches" if e2e_graph is not None else "serial copy, step, copy"},
+                "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3), "api": api,
+                "pipeline": (f"one CUDA graph: metadata H2D, build(), then {NG} layer groups with H2D / layer hooks / D2H on three stream branches"
+                             if e2e_graphed else "metadata H2D, build(), copies and layer hooks issued eagerly")},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "achieved": kern_gbs, "peak": peak, "unit": "GB/s", "frac": kern_gbs / peak,
-                     "traffic": None, "kernel": ("b200attn::decode_tc_kernel" if (fp8 and Hq // Hkv <= 8) else "b200attn::decode_kernel") + " (split-KV paged flash-decoding, in-kernel merge; CUDA graph of one launch per layer cache, PDL off)",
-                     "algorithmic_bytes_per_launch": dec_b, "avg_launch_us": kern_ms * 1e3, "launches_timed": len(evs),
+                     "traffic": None,
+                     "kernel": kname + " (split-KV paged flash-decoding, merge in-kernel); CUDA graph of one launch per layer cache, launched "
+                                       "as the step launches it (programmatic dependent launch on)",
+                     "algorithmic_bytes_per_launch": dec_b, "avg_launch_us": kern[1] * 1e3, "launches_timed": reps * NL,
+                     "pct_of_8tbs": kern_gbs / 8000.0 * 100.0,
+                     "isolated": {"note": "same graph with PDL off: no overlap between neighbouring launches", "avg_launch_us": kern[0] * 1e3,
+                                  "achieved": kern_iso_gbs, "frac": kern_iso_gbs / peak, "pct_of_8tbs": kern_iso_gbs / 8000.0 * 100.0},
                      "peak_source": peak_src},
+        "vs_sm100_reference": sm100,
         "cpu_baseline": cpu,
         "clocks": sampler.summary(),
     }
+    if sharded is not None:
+        line["sharded"] = sharded
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            line["roofline"]["traffic"] = json.load(f).get(args.workload)
+            tr = json.load(f).get(args.workload)
+            if isinstance(tr, dict):
+                line["roofline"]["traffic"] = tr.get("dram_bytes_per_launch")
+                line["roofline"]["traffic_source"] = {k: v for k, v in tr.items() if k != "dram_bytes_per_launch"}
+            else:
+                line["roofline"]["traffic"] = tr
     except Exception:  # noqa: BLE001
         pass
     emit(json.dumps(line))
     if world > 1:
         sys.stdout.flush(); sys.stderr.flush()
         os._exit(0)
+
+
+# ------------------------------------------------------------------------------------------------
+# comparison arms: the reference's GPU kernels through the same step
+# ------------------------------------------------------------------------------------------------
+def run_sm100(args, w):
+    import torch
+
+    from tests.tools import sm100_reference as R
+    from tests.tools.workloads import Problem
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    P = Problem(w, dev, seed=1234, fill="write")
+    NL, B = P.NL, w["B"]
+    arm = args.impl
+    if arm == "flashinfer":
+        dec = R.time_flashinfer(P.phys, P.q, P.bt, P.lens, int(P.lens_np.max()), P.sm_scale, P.k_scale[0].item(), P.v_scale[0].item(),
+                                P.dec_bytes, q_fp8=P.fp8 and not args.fi_q_bf16)
+    else:
+        dec = R.time_triton(P.planes, P.q, P.bt, P.lens, int(P.lens_np.max()), P.sm_scale, P.k_scale, P.v_scale, P.dec_bytes, w["Hkv"])
+    wr = R.time_vllm_kv_write(P.planes, P.kn, P.vn, P.step_slots, P.k_scale, P.v_scale, P.wr_bytes)
+    if "error" in dec or "error" in wr:
+        emit(json.dumps({"impl": arm, "unavailable": (dec.get("error") or wr.get("error"))[:300]}))
+        return
+    dec.pop("out", None)
+    us = dec["us_per_layer"] + wr["us_per_layer"]
+    ms_per_step = us * NL * 1e-3
+    step_bytes = (P.dec_bytes + P.wr_bytes) * NL
+    line = {"impl": arm, "metric": "paged_decode_attn_hbm_gbs", "value": step_bytes / (ms_per_step * 1e-3) / 1e9, "unit": "GB/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "data": "synthetic", "config": workload_config(args, w, 0), "tok_s": B / (ms_per_step * 1e-3),
+            "decode": dec, "kv_write": wr,
+            "note": "comparison arm: the reference's own sm_100 kernels (decode and vLLM's reshape_and_cache_flash timed as separate CUDA "
+                    "graphs of one launch per layer cache and summed); never part of the product path"}
+    emit(json.dumps(line))
 
 
 _REAL_STDOUT = None
@@ -539,19 +660,23 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "flashinfer", "triton"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--ctas", type=int, default=0, help="decode grid override (0 = 2 CTAs/SM)")
     ap.add_argument("--allgather", default="none", choices=["none", "step"], help="NCCL all-gather of head-sharded outputs")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sm100-ref", action="store_true", help="skip timing the reference's own Blackwell kernels")
+    ap.add_argument("--no-sharded", action="store_true", help="N > 1: skip the strong-scaled thinker block")
+    ap.add_argument("--fi-q-bf16", action="store_true", help="--impl flashinfer: keep the query in bf16 (default: fp8 query, as vLLM does)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     w = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, w)
-    else:
+    elif args.impl == "ours":
         run_ours(args, w)
+    else:
+        run_sm100(args, w)
 
 
 if __name__ == "__main__":
