@@ -6,9 +6,10 @@
 Workload (BASELINE.json configs[1], made concrete in SURVEY.md §8d "C2"): Qwen3-TTS talker streaming decode, FP8-e4m3
 KV cache, batch 64, 4k context, (Hq, Hkv, D) = (16, 2, 128), block size 16, 20 layers, synthetic data.
 One STEP = one decode step of the attention path of the whole model, driven through the vLLM plugin classes exactly as
-the reference's runner drives them: `MetadataBuilder.build` once (eager: row buffers + the device-side split-KV plan),
-then for each of the 20 layers `Impl.do_kv_cache_update` (KV write + FP8 quantisation) and `Impl.forward` (split-KV paged
-decode with the merge in-kernel), the 40 layer launches replayed as one CUDA graph like vLLM's FULL cudagraph mode.
+the reference's runner drives them: `MetadataBuilder.build` once (row buffers + the device-side split-KV plan), then for
+each of the 20 layers `Impl.do_kv_cache_update` (KV write + FP8 quantisation) and `Impl.forward` (split-KV paged decode
+with the merge in-kernel), replayed as one CUDA graph (`ms_per_step_eager_build`: build() issued eagerly before a graph
+of the 40 layer launches, which is what vLLM's FULL cudagraph mode does).
 All 20 per-layer caches (2.7 GB) are distinct, so every step streams far more than the 126 MB L2 (no flush needed).
 
 JSON keys (one line, rank 0): see the task contract.
@@ -380,17 +381,22 @@ def run_ours(args, w):
         api = "torch.ops.b200attn.* (vLLM not importable on this box)"
     gathered = torch.empty(world, NL, B, Hq, D, dtype=torch.bfloat16, device=dev) if (world > 1 and args.allgather != "none") else None
 
-    def hooks():
+    def step_body():
+        # build() is capture-safe (two small copies into the builder's fixed buffers + the device-side plan kernel): the whole
+        # step is ONE graph, so the device-timed number does not depend on host enqueue jitter (N ranks share the host cores)
+        S.build()
         S.layers()
         if gathered is not None:
             dist.all_gather_into_tensor(gathered, P.out)
 
     side = torch.cuda.Stream(device=dev)
-    replay, use_graph = (hooks, False) if args.no_graph else capture(hooks, side)
+    step, use_graph = (step_body, False) if args.no_graph else capture(step_body, side)
+    # vLLM itself runs build() eagerly before each replay of a graph that holds only the layer hooks: timed as an extra key
+    hooks_only, _ = (S.layers, False) if (args.no_graph or gathered is not None) else capture(S.layers, side)
 
-    def step():
+    def step_eager_build():
         S.build()
-        replay()
+        hooks_only()
 
     launches_per_step = 1 + 2 * NL   # plan + per layer: kv_write, decode (split-KV partials merged in-kernel)
 
@@ -409,6 +415,7 @@ def run_ours(args, w):
     ms = max_over_ranks(time_region(step, args.steps, barrier), dev, world)
     sampler.active = False
     ms_per_step = ms / args.steps
+    ms_eager_build = max_over_ranks(time_region(step_eager_build, args.steps, barrier), dev, world) / args.steps
     # distribution over >= 100 individually timed steps (20 warm-up + 100 timed, median and p10 / p90)
     n_dist = max(100, args.steps)
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_dist)]
@@ -563,6 +570,7 @@ def run_ours(args, w):
         "tok_s": B / (ms_per_step * 1e-3),
         "pct_of_8tbs": gbs / world / 8000.0 * 100.0, "pct_of_measured_hbm": gbs / world / peak * 100.0,
         "cuda_graph": use_graph,
+        "ms_per_step_eager_build": ms_eager_build,   # build() issued eagerly before each replay of a layers-only graph (vLLM's flow)
         "distribution": dist_ms,
         "e2e": {"value": gbs_e2e, "unit": "GB/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                 "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3), "api": api,
