@@ -18,10 +18,13 @@ What the reference does at each hook, and what we do instead:
   * MetadataBuilder.build -> FlashInfer `plan` / Triton segment buffers (flashinfer.py:886-1248, triton_attn.py:216-268)
                          -> torch.ops.b200attn.decode_plan (device-side, sync-free) into buffers owned by the builder
 
-Rows with more than one query token (spec-decode verification, chunked prefill) are served by the same kernel: every
-query token becomes a decode row with its own causal length and a `row_map` entry pointing at its request's
-block-table row.  That keeps the backend a complete drop-in (correct for any batch vLLM schedules); a dedicated
-prefill kernel is a §8(f) "next" row.
+Requests with more than one query token (chunked prefill, spec-decode verification, mixed batches) go to the tcgen05
+prefill kernel (torch.ops.b200attn.paged_prefill, FP8 KV) while the one-token requests of the same batch stay on the decode
+kernel.  The routing is done ON THE DEVICE: the decode plan gets length 0 for the tokens of multi-token requests, the
+prefill plan gets no tile for the one-token requests, and both kernels are launched over the whole batch -- so nothing
+about the split is a host-side value baked into a captured launch, and no batch reordering is asked of the model runner.
+With a 16-bit KV cache (no tensor-core prefill kernel yet) every query token becomes a decode row with its own causal
+length and a `row_map` entry pointing at its request's block-table row, as in round 1.
 
 There is no fallback to another backend or to the CPU: without libb200attn.so / a CUDA device the ops raise.
 """
@@ -161,13 +164,22 @@ class B200PagedAttentionMetadata:
     slot_mapping: torch.Tensor
     workspace: "ops.DecodeWorkspace"  # plan + split-KV partial buffers (owned by the builder)
     use_cascade: bool = False
+    # mixed batch routed between the two kernels (FP8 KV): rows of multi-token requests have seq_lens == 0 above and are
+    # served by the prefill kernel from the request-level tensors below
+    has_decode: bool = True
+    has_prefill: bool = False
+    num_reqs: int = 0
+    req_seq_lens: torch.Tensor | None = None      # int32 [num_reqs]
+    query_start_loc: torch.Tensor | None = None   # int32 [num_reqs + 1]
+    tile_prefix: torch.Tensor | None = None       # int32 [num_reqs + 1] (builder-owned)
 
 
 class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttentionMetadata]):
     """Builds the split-KV plan once per step on the device (kernel `plan_kernel`, no host sync, no allocation)."""
 
     _cudagraph_support: ClassVar[AttentionCGSupport] = AttentionCGSupport.ALWAYS
-    reorder_batch_threshold: int | None = None   # one kernel serves every row: no decode/prefill reordering needed
+    reorder_batch_threshold: int | None = None   # decode / prefill routing happens on the device: no reordering needed
+    prefill_min_query_len: ClassVar[int] = 2      # requests with at least this many query tokens go to the prefill kernel
 
     def __init__(self, kv_cache_spec, layer_names, vllm_config, device):
         super().__init__(kv_cache_spec, layer_names, vllm_config, device)
@@ -186,6 +198,11 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
         self._row_lens = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
         self._row_map = torch.zeros(self.max_rows, dtype=torch.int32, device=device)
         self._identity = torch.arange(self.max_rows, dtype=torch.int32, device=device)
+        self.max_reqs = int(getattr(vllm_config.scheduler_config, "max_num_seqs", None) or self.max_rows)
+        self._tile_prefix = torch.zeros(self.max_reqs + 1, dtype=torch.int32, device=device)
+        # the tensor-core prefill kernel reads the FP8 cache; 16-bit caches keep the per-token decode rows
+        self.use_prefill_kernel = self.kv_torch_dtype == torch.uint8 and self.head_dim == 128
+        self._capturing = False
 
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
               fast_build: bool = False) -> B200PagedAttentionMetadata:
@@ -197,22 +214,43 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
         T = m.num_actual_tokens
         if T > self.max_rows:
             raise B200AttnError(f"{T} tokens exceed the planned maximum of {self.max_rows}")
-        if m.max_query_len <= 1 and T == m.num_reqs:
+        R = m.num_reqs
+        has_decode, has_prefill = True, False
+        if m.max_query_len <= 1 and T == R:
             self._row_lens[:T].copy_(m.seq_lens[:T])                # pure decode: rows == requests
             self._row_map[:T].copy_(self._identity[:T])
         else:
             lens, rmap = expand_query_rows(m.query_start_loc, m.seq_lens, T)
+            if self.use_prefill_kernel and R <= self.max_reqs:
+                qsl = m.query_start_loc[:R + 1]
+                short = (qsl[1:] - qsl[:-1]) < self.prefill_min_query_len                 # [R] on the device
+                lens = torch.where(short[rmap.long()], lens, torch.zeros_like(lens))       # the prefill kernel's tokens: no decode row
+                torch.ops.b200attn.prefill_plan(qsl, self._tile_prefix, self.num_heads_q, self.num_heads_kv, self.prefill_min_query_len)
+                has_prefill = True
+                if not self._capturing and m.query_start_loc_cpu is not None:
+                    # eager step: skip the launch of a kernel that has no request (host copy of the offsets, no sync)
+                    ql = m.query_start_loc_cpu[1:R + 1] - m.query_start_loc_cpu[:R]
+                    has_decode = bool((ql < self.prefill_min_query_len).any())
+                    has_prefill = bool((ql >= self.prefill_min_query_len).any())
             self._row_lens[:T].copy_(lens)
             self._row_map[:T].copy_(rmap)
         seq_lens, row_map = self._row_lens[:T], self._row_map[:T]
-        self.workspace.make_plan(seq_lens, self.num_heads_q, self.num_heads_kv, m.block_table_tensor, self.block_size, row_map)
+        if has_decode:
+            self.workspace.make_plan(seq_lens, self.num_heads_q, self.num_heads_kv, m.block_table_tensor, self.block_size, row_map)
         return B200PagedAttentionMetadata(
             num_actual_tokens=T, num_rows=T, max_query_len=m.max_query_len, seq_lens=seq_lens,
-            block_table=m.block_table_tensor, row_map=row_map, slot_mapping=m.slot_mapping, workspace=self.workspace)
+            block_table=m.block_table_tensor, row_map=row_map, slot_mapping=m.slot_mapping, workspace=self.workspace,
+            has_decode=has_decode, has_prefill=has_prefill, num_reqs=R, req_seq_lens=m.seq_lens[:R],
+            query_start_loc=m.query_start_loc[:R + 1], tile_prefix=self._tile_prefix[:R + 1])
 
     def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200PagedAttentionMetadata:
-        # the plan kernel reads seq_lens on the device at replay time; nothing is baked in at capture
-        return self.build(0, common_attn_metadata)
+        # the plan kernels read seq_lens / query_start_loc on the device at replay time; nothing about the batch is baked
+        # in at capture, and a captured mixed batch launches BOTH kernels (either may find no work at replay)
+        self._capturing = True
+        try:
+            return self.build(0, common_attn_metadata)
+        finally:
+            self._capturing = False
 
     def use_cascade_attention(self, *args, **kwargs) -> bool:
         return False
@@ -330,15 +368,23 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         k_scale, v_scale = self._scales(layer, query.device)
         q = query[:T].view(T, self.num_heads, self.head_size)
         out = output[:T].view(T, self.num_heads, self.head_size)
-        # fresh_tokens: the KV write that precedes us on the stream touched at most the last max_query_len positions
-        md.workspace.decode(q, k_cache, v_cache, md.block_table, md.seq_lens, out, k_scale, v_scale, self.scale,
-                            row_map=md.row_map, fresh_tokens=max(1, md.max_query_len), fused_merge=True)
+        if md.has_decode:
+            # fresh_tokens: the KV write that precedes us on the stream touched at most the last max_query_len positions of
+            # a decode row's sequence (1 when the multi-token requests are the prefill kernel's)
+            fresh = 1 if md.has_prefill else max(1, md.max_query_len)
+            md.workspace.decode(q, k_cache, v_cache, md.block_table, md.seq_lens, out, k_scale, v_scale, self.scale,
+                                row_map=md.row_map, fresh_tokens=fresh, fused_merge=True)
+        if md.has_prefill:
+            torch.ops.b200attn.paged_prefill(q, k_cache, v_cache, md.block_table, md.req_seq_lens, md.query_start_loc,
+                                             md.tile_prefix, out, k_scale, v_scale, self.scale, 0)
         return output
 
     def forward_with_lse(self, layer, query, kv_cache, attn_metadata, output, lse) -> None:
         """Decode returning the natural-log LSE per (row, head): the per-rank piece of a sequence-split (DCP) exchange,
         combined across ranks by torch.ops.b200attn.merge_lse (replaces cp_lse_ag_out_rs, flashinfer.py:1714-1738)."""
         md = attn_metadata
+        if md.has_prefill:
+            raise NotImplementedError("forward_with_lse serves decode rows only (the prefill kernel returns no LSE)")
         T = md.num_actual_tokens
         k_cache, v_cache = self._planes(kv_cache)
         k_scale, v_scale = self._scales(layer, query.device)

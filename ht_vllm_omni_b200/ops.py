@@ -247,6 +247,69 @@ def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_sc
 
 
 # ------------------------------------------------------------------------------------------------
+# paged_prefill: varlen causal attention for rows with q_len > 1 (chunked prefill, mixed batches, spec-decode verification)
+# ------------------------------------------------------------------------------------------------
+def prefill_tile_tokens(num_q_heads: int, num_kv_heads: int) -> int:
+    """Query tokens per 128-row tile of the prefill kernel (128 / query heads per kv head)."""
+    n = load_library().b200attn_prefill_tile_tokens(num_q_heads, num_kv_heads)
+    if n <= 0:
+        raise B200AttnError(f"prefill: unsupported head counts Hq={num_q_heads} Hkv={num_kv_heads}")
+    return n
+
+
+@torch.library.custom_op("b200attn::prefill_plan", mutates_args=("tile_prefix",), device_types="cuda")
+def prefill_plan(query_start_loc: torch.Tensor, tile_prefix: torch.Tensor, num_q_heads: int, num_kv_heads: int,
+                 min_query_len: int = 1) -> None:
+    """tile_prefix[num_reqs + 1] = exclusive scan of each request's query-tile count (0 for requests with fewer than
+    `min_query_len` query tokens: the decode kernel's rows in a mixed batch).  Once per scheduler step."""
+    _require_cuda(query_start_loc, tile_prefix)
+    n = query_start_loc.shape[0] - 1
+    if n <= 0:
+        return
+    if query_start_loc.dtype != torch.int32 or tile_prefix.dtype != torch.int32 or not query_start_loc.is_contiguous() \
+            or not tile_prefix.is_contiguous() or tile_prefix.numel() < n + 1:
+        raise B200AttnError("query_start_loc / tile_prefix must be contiguous int32 ([num_reqs + 1])")
+    check(load_library().b200attn_prefill_plan(query_start_loc.data_ptr(), n, num_q_heads, num_kv_heads, int(min_query_len),
+                                               tile_prefix.data_ptr(), _stream(tile_prefix)), "b200attn_prefill_plan")
+
+
+@prefill_plan.register_fake
+def _(query_start_loc, tile_prefix, num_q_heads, num_kv_heads, min_query_len=1) -> None:
+    return None
+
+
+@torch.library.custom_op("b200attn::paged_prefill", mutates_args=("out",), device_types="cuda")
+def paged_prefill(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
+                  seq_lens: torch.Tensor, query_start_loc: torch.Tensor, tile_prefix: torch.Tensor, out: torch.Tensor,
+                  k_scale: torch.Tensor, v_scale: torch.Tensor, sm_scale: float, first_token: int = 0) -> None:
+    """query / out [T, Hq, D]; block_table [R, max_blocks], seq_lens [R], query_start_loc [R + 1], tile_prefix [R + 1]
+    describe the R requests whose tokens are query[qsl[r] - first_token : qsl[r + 1] - first_token]; token t of a request's
+    chunk attends to cache positions [0, seq_len - q_len + t + 1).  FP8 e4m3 cache only."""
+    _require_cuda(query, k_cache, v_cache, block_table, seq_lens, query_start_loc, tile_prefix, out)
+    R, T = seq_lens.shape[0], query.shape[0]
+    if R == 0 or T == 0:
+        return
+    (sb, ss, sh), kvdt, sstride = _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale)
+    if query_start_loc.dtype != torch.int32 or tile_prefix.dtype != torch.int32 or query_start_loc.shape[0] < R + 1 \
+            or tile_prefix.numel() < R + 1 or not query_start_loc.is_contiguous() or not seq_lens.is_contiguous():
+        raise B200AttnError("query_start_loc / tile_prefix must be contiguous int32 [num_reqs + 1]")
+    if out.shape[0] < T or block_table.shape[0] < R:
+        raise B200AttnError("out / block_table must cover every query token / request")
+    check(load_library().b200attn_prefill(
+        query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1),
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, k_cache.shape[0], block_table.data_ptr(), block_table.stride(0),
+        seq_lens.data_ptr(), query_start_loc.data_ptr(), R, T, int(first_token), query.shape[1], k_cache.shape[2], query.shape[2],
+        k_cache.shape[1], _dt(query), kvdt, float(sm_scale), k_scale.data_ptr(), v_scale.data_ptr(), sstride,
+        tile_prefix.data_ptr(), _stream(query)), "b200attn_prefill")
+
+
+@paged_prefill.register_fake
+def _(query, k_cache, v_cache, block_table, seq_lens, query_start_loc, tile_prefix, out, k_scale, v_scale, sm_scale,
+      first_token=0) -> None:
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
 # merge_lse: combine P attention results by log-sum-exp (sequence-split across shards / ranks)
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("b200attn::merge_lse", mutates_args=("out", "lse_out"), device_types="cuda")

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 3
+#define B200ATTN_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -220,6 +220,42 @@ B200ATTN_API int b200attn_merge_lse_peers(const void* const* parts_o_ptrs, const
                              int32_t num_parts, int64_t o_offset, int64_t lse_offset,
                              void* out, float* lse_out, int32_t n, int32_t num_q_heads,
                              int32_t head_dim, int32_t dtype, void* stream);
+
+/*
+ * Prefill / mixed-batch rows (q_len > 1): varlen causal flash-attention forward over the paged FP8 (e4m3) cache.
+ * Replaces the prefill branch of AttentionImpl.forward: kernel_unified_attention with q_len > 1
+ * ($VLLM/v1/attention/ops/triton_unified_attention.py:286-303, 440-545) and FlashInfer's
+ * trtllm_batch_context_with_kv_cache ($VLLM/v1/attention/backends/flashinfer.py:1500-1689).  A query token at position
+ * t of a request's chunk of q_len tokens attends to cache positions [0, seq_len - q_len + t + 1).
+ *
+ *   b200attn_prefill_tile_tokens  query tokens per 128-row tile (128 / query heads per kv head; 0 for unsupported heads)
+ *   b200attn_prefill_plan         tile_prefix[num_reqs + 1] (int32, device) = exclusive scan of ceil(q_len / tile_tokens) over
+ *                                 the requests with q_len >= min_query_len (the others get no tile: in a mixed batch the
+ *                                 decode kernel serves them, so the routing needs no host-side split and no batch
+ *                                 reordering); once per scheduler step (shared by all layers), capture-safe, no host sync
+ *   b200attn_prefill              one launch: grid = (ceil(num_tokens / tile_tokens) + num_reqs) * kv heads CTAs (host-side
+ *                                 bound, surplus CTAs exit), tcgen05 (kind::f8f6f4) S = Q.K^T and O += P.V with TMEM accumulators.
+ *
+ * seq_lens / query_start_loc / block_table / tile_prefix are the rows of the requests being prefilled (pointers pre-offset by
+ * the caller when decode rows come first); q and out are the full [tokens, heads, head_dim] tensors and `first_token` is
+ * subtracted from every query_start_loc entry before indexing them (pass query_start_loc[first request] when q / out are
+ * pre-offset, else 0).  `num_tokens` bounds the grid: the number of query tokens covered by these requests.
+ * fp8_e4m3 cache, bf16 / fp16 q and out, head_dim 128, per-tensor (scale_stride 0) or per-head (1) scales.
+ */
+B200ATTN_API int b200attn_prefill_tile_tokens(int32_t num_q_heads, int32_t num_kv_heads);
+B200ATTN_API int b200attn_prefill_plan(const int32_t* query_start_loc, int32_t num_reqs, int32_t num_q_heads,
+                                       int32_t num_kv_heads, int32_t min_query_len, int32_t* tile_prefix, void* stream);
+B200ATTN_API int b200attn_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+                                  void* out, int64_t out_stride_t, int64_t out_stride_h,
+                                  const void* k_cache, const void* v_cache,
+                                  int64_t stride_block, int64_t stride_slot, int64_t stride_head, int64_t num_blocks,
+                                  const int32_t* block_table, int64_t block_table_stride,
+                                  const int32_t* seq_lens, const int32_t* query_start_loc,
+                                  int32_t num_reqs, int32_t num_tokens, int32_t first_token,
+                                  int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                                  int32_t q_dtype, int32_t kv_dtype, float sm_scale,
+                                  const float* k_scale, const float* v_scale, int32_t scale_stride,
+                                  const int32_t* tile_prefix, void* stream);
 
 /*
  * KV hand-off gather (the step after the path).

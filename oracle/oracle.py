@@ -13,6 +13,7 @@ docs/getting_started/quickstart.md:22; this image carries vllm 0.22.0), so each 
   paged_decode_ref      $VLLM/v1/attention/ops/triton_unified_attention.py:38-55 (dequant), :395-545 (tile loop),
                         triton_attention_helpers.py:361-383 (softmax_step), :606-643 (2D epilogue)
   paged_decode_split_ref  same kernel, IS_3D path :297-300,:547-600 + reduce_segments :645-733
+  paged_prefill_ref     same kernel with q_len > 1: :286-303 (causal length per query row), :511-520 (mask)
   merge_lse_ref         $VLLM/v1/attention/ops/merge_attn_states.py:7-101
 
 Pinning: the reference's own tests hold NO golden vector for this boundary.  The oracle is pinned
@@ -333,6 +334,58 @@ def paged_decode_exact(q, k_cache, v_cache, block_table, seq_lens, sm_scale, k_s
             P = np.exp(S)
             out[b, h * G:(h + 1) * G] = (P @ V) / P.sum(axis=1, keepdims=True)
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# paged prefill / mixed-batch attention (q_len >= 1 per request, causal)
+# ------------------------------------------------------------------------------------------------
+
+
+def paged_prefill_ref(q, query_start_loc, k_cache, v_cache, block_table, seq_lens, sm_scale, k_scale=None, v_scale=None,
+                      fp8=False, act="bf16", exact=False, rows=None):
+    """kernel_unified_attention with q_len > 1 ($VLLM/v1/attention/ops/triton_unified_attention.py): query token t of request
+    r (q_len = qsl[r+1] - qsl[r] tokens, the LAST q_len positions of its seq_len) attends to cache positions
+    [0, context_len + t + 1) with context_len = seq_len - q_len (:286-303 and the causal mask :511-520); dequant, softmax and
+    P.to(V.dtype) @ V as in paged_decode_ref (one tile spanning the row: the tile size only changes fp32 summation order).
+    q float32 [T, Hq, D] (activation-representable) -> float32 [T, Hq, D] rounded to `act`.
+    exact=True: float64 with no intermediate rounding and an unrounded result (the accuracy yardstick).
+    rows: optional iterable of token indices to evaluate (others stay 0) -- full-size cases sample rows."""
+    T, Hq, D = q.shape
+    bs, Hkv = k_cache.shape[1], k_cache.shape[2]
+    G = Hq // Hkv
+    ft = np.float64 if exact else np.float32
+    ks = np.broadcast_to(np.asarray(1.0 if k_scale is None else k_scale, dtype=ft).reshape(-1), (Hkv,))
+    vs = np.broadcast_to(np.asarray(1.0 if v_scale is None else v_scale, dtype=ft).reshape(-1), (Hkv,))
+    out = np.zeros((T, Hq, D), dtype=ft)
+    want = None if rows is None else set(int(t) for t in rows)
+    for r in range(len(seq_lens)):
+        q0, q1 = int(query_start_loc[r]), int(query_start_loc[r + 1])
+        L, ql = int(seq_lens[r]), q1 - q0
+        if ql <= 0 or L <= 0:
+            continue
+        toks = [t for t in range(ql) if want is None or (q0 + t) in want]
+        if not toks:
+            continue
+        ctx = L - ql
+        Lmax = min(L, ctx + max(toks) + 1)
+        lim = np.minimum(L, ctx + np.asarray(toks) + 1)                                  # [n]
+        mask = np.arange(Lmax)[None, :] < lim[:, None]                                   # [n, Lmax]
+        for h in range(Hkv):
+            Kr, Vr = _gather(k_cache, block_table[r], Lmax, h, bs), _gather(v_cache, block_table[r], Lmax, h, bs)
+            if exact:
+                K = (e4m3_decode(Kr).astype(ft) * ks[h]) if fp8 else Kr.astype(ft)
+                V = (e4m3_decode(Vr).astype(ft) * vs[h]) if fp8 else Vr.astype(ft)
+            else:
+                K, V = _dequant(Kr, ks[h], fp8, act), _dequant(Vr, vs[h], fp8, act)
+            for g in range(G):
+                hq = h * G + g
+                S = ft(sm_scale) * (q[[q0 + t for t in toks], hq].astype(ft) @ K.T)       # [n, Lmax]
+                S = np.where(mask, S, -np.inf)
+                P = np.exp(S - S.max(axis=1, keepdims=True)).astype(ft)
+                den = P.sum(axis=1, keepdims=True, dtype=ft)
+                Pv = P if exact else act_round(P, act)
+                out[[q0 + t for t in toks], hq] = (Pv @ V).astype(ft) / den
+    return out if exact else act_round(out, act)
 
 
 # ------------------------------------------------------------------------------------------------
