@@ -132,6 +132,19 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
 __device__ __forceinline__ void st_cluster_f32x2(uint32_t addr, float a, float b) {
   asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
 }
+// asynchronous stores into another CTA's shared memory that carry their own completion: each one adds its byte count to the
+// transaction count of an mbarrier in the DESTINATION CTA, so the receiver's wait on that barrier is the only ordering
+// needed -- no fence or release by the sender (its threads never wait for the stores to be performed)
+__device__ __forceinline__ void st_async_f32x4(uint32_t addr, float a, float b, float c, float d, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(addr), "f"(a),
+               "f"(b), "f"(c), "f"(d), "r"(remote_bar)
+               : "memory");
+}
+__device__ __forceinline__ void st_async_f32x2(uint32_t addr, float a, float b, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(addr), "f"(a), "f"(b),
+               "r"(remote_bar)
+               : "memory");
+}
 // arrive (count 1) on an mbarrier in another CTA of the cluster; release at cluster scope orders this thread's earlier
 // (and, through CTA barriers, its CTA's earlier) distributed-shared-memory stores before it
 __device__ __forceinline__ void mbar_arrive_remote_release(uint32_t remote_bar) {

@@ -415,7 +415,6 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       float* mrg = scratch + 88;                               // merge scratch (64 floats)
       volatile int* hand = reinterpret_cast<volatile int*>(scratch + 152);
       volatile unsigned long long* pub_req = reinterpret_cast<volatile unsigned long long*>(scratch + 156);   // request ring [1 + 8]
-      const float* recv_o = reinterpret_cast<const float*>(gen + TcSmem::kRecv);   // [8][128]
       const float2* recv_ml = reinterpret_cast<const float2*>(gen + TcSmem::kRecv + 8 * kD * 4);
       const int tpc = cx.w;
       MergeTicket tk = {};
@@ -507,6 +506,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
               seg_mode = in_cluster ? 3 : 2;
               seg_recv = in_cluster && (int)blockIdx.x < ml.c_hi;   // a piece behind us pushes its fold to us
               seg_push = in_cluster && (int)blockIdx.x > ml.c_lo;   // we push ours to the piece before us
+              if (seg_recv && tid == 0) mbar_arrive_expect_tx(recv_bar, kTcRecvBytes);   // the push is kTcRecvBytes of st.async
             }
           }
         }
@@ -667,15 +667,21 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
               // ---- the pair's pieces all sit in this cluster: fold them along the chain c_hi -> ... -> c_lo through
               // distributed shared memory (one push + one mbarrier arrive per hop; no L2 round trips, no atomics) ----
               const int me = (int)blockIdx.x;
-              if (seg_recv) {   // receive the fold of the pieces behind us
+              if (seg_recv) {   // receive the fold of the pieces behind us (its bytes were announced at the segment's start)
                 while (!mbar_try_wait_acq_cluster(recv_bar, 0)) {
                 }
                 if (kDbg && tid == 0) dbg_stamp(p, 12);
+                float rov[8];
+                {
+                  const uint4 r0 = lds128(base + TcSmem::kRecv + d * 32), r1 = lds128(base + TcSmem::kRecv + d * 32 + 16);
+                  rov[0] = __uint_as_float(r0.x); rov[1] = __uint_as_float(r0.y); rov[2] = __uint_as_float(r0.z); rov[3] = __uint_as_float(r0.w);
+                  rov[4] = __uint_as_float(r1.x); rov[5] = __uint_as_float(r1.y); rov[6] = __uint_as_float(r1.z); rov[7] = __uint_as_float(r1.w);
+                }
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                   if (i < p.G) {
                     const float2 rml = recv_ml[i];
-                    const float ro = recv_o[i * kD + d];
+                    const float ro = rov[i];
                     const float mn = fmaxf(mgv[i], rml.x);
                     const float a = (mgv[i] == ninf) ? 0.f : fast_exp2(mgv[i] - mn);
                     const float bsc = (rml.x == ninf) ? 0.f : fast_exp2(rml.x - mn);
@@ -686,17 +692,16 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
                 }
               }
               if (seg_push) {   // push to the piece before us
+                // st.async: every store carries its own completion to the peer's "partial received" barrier (which expects
+                // kTcRecvBytes), so nobody here fences, syncs or waits for the stores to be performed
                 const uint32_t peer = cluster_ctarank() - 1;
                 const uint32_t ro = mapa_shared(base + TcSmem::kRecv, peer);
+                const uint32_t rb = mapa_shared(recv_bar, peer);
+                st_async_f32x4(ro + (uint32_t)d * 32, accv[0], accv[1], accv[2], accv[3], rb);        // layout [head dim][8 heads]
+                st_async_f32x4(ro + (uint32_t)d * 32 + 16, accv[4], accv[5], accv[6], accv[7], rb);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  if (i < p.G) {
-                    st_cluster_f32(ro + (uint32_t)(i * kD + d) * 4, accv[i]);
-                    if (d == i) st_cluster_f32x2(ro + 8 * kD * 4 + (uint32_t)i * 8, mgv[i], lgv[i]);
-                  }
-                }
-                named_bar_sync(1, 128);   // every thread's stores are issued; the release below is cumulative over them
-                if (tid == 0) mbar_arrive_remote_release(mapa_shared(recv_bar, peer));
+                for (int i = 0; i < 8; ++i)
+                  if (d == i) st_async_f32x2(ro + 8 * kD * 4 + (uint32_t)i * 8, mgv[i], lgv[i], rb);
                 if (kDbg && tid == 0) dbg_stamp(p, 13);
               } else {
                 store_final();
