@@ -295,6 +295,7 @@ class PluginStep:
         B, Hq, Hkv, D, bs = w["B"], w["Hq"], w["Hkv"], w["D"], w["bs"]
         self.P, self.B, self.Hq, self.Hkv, self.D = P, B, Hq, Hkv, D
         be = BK.B200PagedAttentionBackend
+        self.fwd_writes = bool(be.forward_includes_kv_cache_update)
         self.impl = be.get_impl_cls()(Hq, D, P.sm_scale, Hkv, None, None, "fp8" if P.fp8 else "auto")
         self.layer = types.SimpleNamespace(_k_scale=P.k_scale, _v_scale=P.v_scale, _k_scale_float=1.0, _v_scale_float=1.0)
         mc = types.SimpleNamespace(get_num_attention_heads=lambda pc: Hq, get_num_kv_heads=lambda pc: Hkv, get_head_size=lambda: D)
@@ -314,7 +315,8 @@ class PluginStep:
 
     def layers(self, lo=0, hi=None):
         for l in range(lo, self.P.NL if hi is None else hi):
-            self.impl.do_kv_cache_update(self.layer, self.k2[l], self.v2[l], self.kv_caches[l], self.cm.slot_mapping)
+            if not self.fwd_writes:   # attention.py:493: a backend whose forward() includes the KV write gets no separate update call
+                self.impl.do_kv_cache_update(self.layer, self.k2[l], self.v2[l], self.kv_caches[l], self.cm.slot_mapping)
             self.impl.forward(self.layer, self.q2[l], self.k2[l], self.v2[l], self.kv_caches[l], self.md, self.o2[l])
 
     @property
@@ -374,7 +376,9 @@ def run_ours(args, w):
     P = Problem(w, dev, seed=1234 + rank, fill="write")   # caches filled THROUGH the write path from N(0,1) tokens
     try:
         S = PluginStep(P, dev)
-        api = "vLLM plugin classes: B200PagedAttentionMetadataBuilder.build + Impl.do_kv_cache_update + Impl.forward per layer"
+        api = ("vLLM plugin classes: B200PagedAttentionMetadataBuilder.build + Impl.forward per layer (forward_includes_kv_cache_update: "
+               "the decode launch writes the step's tokens itself)" if S.fwd_writes else
+               "vLLM plugin classes: B200PagedAttentionMetadataBuilder.build + Impl.do_kv_cache_update + Impl.forward per layer")
     except Exception as e:  # noqa: BLE001
         print(f"# vLLM plugin classes unavailable ({type(e).__name__}: {str(e)[:200]}); driving torch.ops.b200attn directly", file=sys.stderr)
         S = OpsStep(P, dev)
@@ -398,7 +402,9 @@ def run_ours(args, w):
         S.build()
         hooks_only()
 
-    launches_per_step = 1 + 2 * NL   # plan + per layer: kv_write, decode (split-KV partials merged in-kernel)
+    fwd_writes = bool(getattr(S, "fwd_writes", False)) and P.fp8 and Hq // Hkv <= 8
+    # plan + per layer: decode with the KV write and the split-KV merge in-kernel, or kv_write + decode
+    launches_per_step = 1 + (1 if fwd_writes else 2) * NL
 
     def barrier():
         if world > 1:
@@ -487,7 +493,11 @@ def run_ours(args, w):
     def decode_only():
         for l in range(NL):
             kc, vc = P.planes[l]
-            ws.decode(P.q[l], kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale, P.sm_scale, fresh_tokens=1)
+            if fwd_writes:   # the launch the step issues: decode that also stores the rows' new tokens
+                ws.decode_kv_write(P.q[l], P.kn[l], P.vn[l], P.step_slots, kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale,
+                                   P.sm_scale, fresh_tokens=1)
+            else:
+                ws.decode(P.q[l], kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale, P.sm_scale, fresh_tokens=1)
 
     reps = max(3, min(args.steps, 20))
     kern = {}
@@ -523,8 +533,16 @@ def run_ours(args, w):
                                "(FlashInfer enables programmatic dependent launch on sm_100 by itself; so does our step); ratio_vs_ours = arm "
                                "time / our time (`ours_us`, PDL on), > 1 means ours is faster", "ours_us": kern[1] * 1e3,
                      "ours_isolated_pdl_off_us": kern[0] * 1e3}
+            # the reference's whole per-layer path next to ours (what a layer of the model pays for this path)
+            fi8, qq, wrr = arms.get("flashinfer_trtllm_gen_q_fp8", {}), arms.get("vllm_query_fp8_quant", {}), arms.get("vllm_reshape_and_cache_flash", {})
+            if all("us_per_layer" in a for a in (fi8, qq, wrr)):
+                sm100["layer_path_us"] = {
+                    "reference_flashinfer_fp8_query": fi8["us_per_layer"] + qq["us_per_layer"] + wrr["us_per_layer"],
+                    "reference_parts": "trtllm_batch_decode (fp8 q) + scaled_fp8_quant(q) + reshape_and_cache_flash, each timed in its own graph",
+                    "ours": ms_per_step * 1e3 / NL,
+                    "ours_parts": "ms_per_step / layers (plan included): " + ("decode launch that also writes the KV" if fwd_writes else "kv_write + decode")}
             for k, v in arms.items():
-                if "us_per_layer" in v and not k.startswith("vllm_reshape"):
+                if "us_per_layer" in v and not k.startswith("vllm_"):
                     v["ratio_vs_ours"] = v["us_per_layer"] / (kern[1] * 1e3)
                 sm100[k] = v
         except Exception as e:  # noqa: BLE001
@@ -579,7 +597,8 @@ def run_ours(args, w):
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "achieved": kern_gbs, "peak": peak, "unit": "GB/s", "frac": kern_gbs / peak,
                      "traffic": None,
-                     "kernel": kname + " (split-KV paged flash-decoding, merge in-kernel); CUDA graph of one launch per layer cache, launched "
+                     "kernel": kname + (" (split-KV paged flash-decoding, KV write and merge in-kernel)" if fwd_writes else
+                                        " (split-KV paged flash-decoding, merge in-kernel)") + "; CUDA graph of one launch per layer cache, launched "
                                        "as the step launches it (programmatic dependent launch on)",
                      "algorithmic_bytes_per_launch": dec_b, "avg_launch_us": kern[1] * 1e3, "launches_timed": reps * NL,
                      "pct_of_8tbs": kern_gbs / 8000.0 * 100.0,

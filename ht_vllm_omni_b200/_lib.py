@@ -13,7 +13,7 @@ DT_BF16, DT_FP16, DT_FP8_E4M3 = 0, 1, 2
 TILE_TOKENS = 64
 MAX_GROUP = 16
 MAX_CTAS = 1024
-ABI_VERSION = 4
+ABI_VERSION = 5
 DECODE_FUSED_MERGE = 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -47,6 +47,9 @@ PROTOTYPES = {
     "b200attn_workspace_bytes": (_sz, [_i32, _i32]),
     "b200attn_decode": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _p, _i32,
                                   _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32, _p, _sz, _p, _p, _i32, _i32, _p]),
+    "b200attn_decode_kv_write": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _i64, _i64, _i64,
+                                           _i64, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32,
+                                           _p, _sz, _p, _p, _i32, _i32, _p]),
     "b200attn_merge": (C.c_int, [_p, _i32, _p, _p, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p]),
     "b200attn_merge_lse": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
     "b200attn_merge_lse_peers": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),

@@ -30,6 +30,7 @@ There is no fallback to another backend or to the CPU: without libb200attn.so / 
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import ClassVar
 
@@ -83,9 +84,13 @@ class B200PagedAttentionBackend(AttentionBackend):
     accept_output_buffer: bool = True
     supported_dtypes: ClassVar[list[torch.dtype]] = [torch.float16, torch.bfloat16]
     supported_kv_cache_dtypes: ClassVar[list[str]] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3"]
-    # the KV write is its own custom op (unified_kv_cache_update), as the reference's runner expects
-    # (vllm_omni/worker/gpu_ar_model_runner.py:231-244)
-    forward_includes_kv_cache_update: bool = False
+    # forward() writes the step's new tokens itself: on a pure-decode step the store happens INSIDE the decode kernel
+    # (b200attn_decode_kv_write: one launch per layer, no kernel boundary between the write and the read); the reference's
+    # runner then hands forward() the unpadded slot_mapping (vllm_omni/worker/gpu_ar_model_runner.py:231-244, the same switch
+    # as $VLLM/v1/worker/gpu_model_runner.py:4097-4104).  B200ATTN_SEPARATE_KV_UPDATE=1 restores the two-op contract
+    # (unified_kv_cache_update -> do_kv_cache_update, then forward), which is also what vLLM's RoPE + KV-cache fusion pass
+    # needs to find (do_rope_and_kv_cache_update below).
+    forward_includes_kv_cache_update: bool = os.environ.get("B200ATTN_SEPARATE_KV_UPDATE", "0") != "1"
 
     @staticmethod
     def get_name() -> str:
@@ -164,6 +169,7 @@ class B200PagedAttentionMetadata:
     slot_mapping: torch.Tensor
     workspace: "ops.DecodeWorkspace"  # plan + split-KV partial buffers (owned by the builder)
     use_cascade: bool = False
+    pure_decode: bool = False         # one query token per request and rows == requests (host-known: max_query_len, counts)
     # mixed batch routed between the two kernels (FP8 KV): rows of multi-token requests have seq_lens == 0 above and are
     # served by the prefill kernel from the request-level tensors below
     has_decode: bool = True
@@ -180,6 +186,17 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
     _cudagraph_support: ClassVar[AttentionCGSupport] = AttentionCGSupport.ALWAYS
     reorder_batch_threshold: int | None = None   # decode / prefill routing happens on the device: no reordering needed
     prefill_min_query_len: ClassVar[int] = 2      # requests with at least this many query tokens go to the prefill kernel
+
+    @classmethod
+    def get_cudagraph_support(cls, vllm_config, kv_cache_spec) -> AttentionCGSupport:
+        """Two-op contract: every launch reads the builder's fixed buffers, so one FULL graph serves any batch (ALWAYS).
+        When forward() owns the KV write, a pure-decode step takes the in-kernel-write launch, which is only valid for one
+        token per request -- a host-side choice that a captured graph would freeze.  FULL graphs are therefore offered for
+        uniform single-token decode batches only (what FlashInfer's TRT-LLM decode path declares too,
+        $VLLM/v1/attention/backends/flashinfer.py); mixed batches run the hooks eagerly between piecewise graphs."""
+        if B200PagedAttentionBackend.forward_includes_kv_cache_update:
+            return AttentionCGSupport.UNIFORM_SINGLE_TOKEN_DECODE
+        return cls._cudagraph_support
 
     def __init__(self, kv_cache_spec, layer_names, vllm_config, device):
         super().__init__(kv_cache_spec, layer_names, vllm_config, device)
@@ -216,7 +233,8 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
             raise B200AttnError(f"{T} tokens exceed the planned maximum of {self.max_rows}")
         R = m.num_reqs
         has_decode, has_prefill = True, False
-        if m.max_query_len <= 1 and T == R:
+        pure = m.max_query_len <= 1 and T == R
+        if pure:
             self._row_lens[:T].copy_(m.seq_lens[:T])                # pure decode: rows == requests
             self._row_map[:T].copy_(self._identity[:T])
         else:
@@ -240,7 +258,7 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
         return B200PagedAttentionMetadata(
             num_actual_tokens=T, num_rows=T, max_query_len=m.max_query_len, seq_lens=seq_lens,
             block_table=m.block_table_tensor, row_map=row_map, slot_mapping=m.slot_mapping, workspace=self.workspace,
-            has_decode=has_decode, has_prefill=has_prefill, num_reqs=R, req_seq_lens=m.seq_lens[:R],
+            pure_decode=pure, has_decode=has_decode, has_prefill=has_prefill, num_reqs=R, req_seq_lens=m.seq_lens[:R],
             query_start_loc=m.query_start_loc[:R + 1], tile_prefix=self._tile_prefix[:R + 1])
 
     def build_for_cudagraph_capture(self, common_attn_metadata: CommonAttentionMetadata) -> B200PagedAttentionMetadata:
@@ -334,8 +352,9 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
 
     def fused_rope_kvcache_supported(self) -> bool:
         """vLLM's RoPE+KV-cache fusion pass ($VLLM/compilation/passes/fusion/rope_kvcache_fusion.py:50) asks the impl; ours
-        does both in one launch (csrc/rope_kv_write.cu).  KV-sharing layers keep the unfused path (they write no cache)."""
-        return self.kv_sharing_target_layer_name is None
+        does both in one launch (csrc/rope_kv_write.cu).  KV-sharing layers keep the unfused path (they write no cache).
+        The pass rewrites rotary_embedding + unified_kv_cache_update, an op that only exists under the two-op contract."""
+        return self.kv_sharing_target_layer_name is None and not B200PagedAttentionBackend.forward_includes_kv_cache_update
 
     def do_rope_and_kv_cache_update(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
                                     positions: torch.Tensor, cos_sin_cache: torch.Tensor, is_neox: bool,
@@ -368,6 +387,17 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         k_scale, v_scale = self._scales(layer, query.device)
         q = query[:T].view(T, self.num_heads, self.head_size)
         out = output[:T].view(T, self.num_heads, self.head_size)
+        if (B200PagedAttentionBackend.forward_includes_kv_cache_update and key is not None and value is not None
+                and self.kv_sharing_target_layer_name is None):
+            # this backend's forward() owns the KV write (attention.py:493 skips unified_kv_cache_update for it)
+            k_new = key[:T].view(T, self.num_kv_heads, self.head_size)
+            v_new = value[:T].view(T, self.num_kv_heads, self.head_size)
+            if md.pure_decode:
+                # one token per request: the decode launch stores each row's token right before it reads the row's last tile
+                md.workspace.decode_kv_write(q, k_new, v_new, md.slot_mapping[:T], k_cache, v_cache, md.block_table, md.seq_lens,
+                                             out, k_scale, v_scale, self.scale, row_map=None, fresh_tokens=1, fused_merge=True)
+                return output
+            torch.ops.b200attn.kv_write(k_new, v_new, k_cache, v_cache, md.slot_mapping[:T], k_scale, v_scale)
         if md.has_decode:
             # fresh_tokens: the KV write that precedes us on the stream touched at most the last max_query_len positions of
             # a decode row's sequence (1 when the multi-token requests are the prefill kernel's)

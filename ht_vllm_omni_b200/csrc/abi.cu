@@ -15,6 +15,7 @@ static int g_opt_pdl = 1;
 static int g_opt_force_simt = 0;
 static int g_opt_debug = 0;
 static int g_opt_tc = 1;
+static int g_opt_fused_write = 1;   // b200attn_decode_kv_write writes the new token inside the decode kernel when it can
 static int g_opt_cluster = 2;   // thread-block cluster size of the tcgen05 decode kernel (1 = no clusters)
 static unsigned long long* g_dbg_buf = nullptr;
 
@@ -36,6 +37,7 @@ int option_force_simt() { return g_opt_force_simt; }
 int option_debug() { return g_opt_debug; }
 int option_tc() { return g_opt_tc; }
 int option_cluster() { return g_opt_cluster; }
+int option_fused_write() { return g_opt_fused_write; }
 unsigned long long* option_debug_buffer() { return g_dbg_buf; }
 
 int launch_with_pdl_cluster(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args, int cluster) {
@@ -154,6 +156,7 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
   else if (!strcmp(name, "debug")) slot = &g_opt_debug;
   else if (!strcmp(name, "tc")) slot = &g_opt_tc;
   else if (!strcmp(name, "cluster")) slot = &g_opt_cluster;
+  else if (!strcmp(name, "fused_write")) slot = &g_opt_fused_write;
   if (!slot) {
     set_error("set_option: unknown option '%s'", name);
     return B200ATTN_EINVAL;

@@ -556,6 +556,7 @@ int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaSt
 int option_force_simt();
 int option_debug();
 int option_tc();
+int option_fused_write();
 int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, DecodeParams& p, int grid, int q_dtype, cudaStream_t stream);
 unsigned long long* option_debug_buffer();
 
@@ -585,14 +586,23 @@ int decode_smem_bytes(int kv_dtype, int nt) {
 
 using namespace b200attn;
 
-extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t,
-                               int64_t out_stride_h, const void* k_cache, const void* v_cache, int64_t stride_block,
-                               int64_t stride_slot, int64_t stride_head, int64_t num_blocks, const int32_t* block_table,
-                               int64_t block_table_stride, const int32_t* seq_lens, int32_t num_seqs, int32_t num_q_heads,
-                               int32_t num_kv_heads, int32_t head_dim, int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
-                               float sm_scale, const float* k_scale, const float* v_scale, int32_t scale_stride,
-                               const void* plan, int32_t num_ctas, void* workspace, size_t workspace_bytes,
-                               float* lse_out, const int32_t* row_map, int32_t fresh_tokens, int32_t flags, void* stream) {
+// the new token of every row, for the decode launch that also writes the cache (b200attn_decode_kv_write)
+struct NewTokens {
+  const void* key;
+  const void* value;
+  int64_t key_stride_t, key_stride_h, value_stride_t, value_stride_h;
+  const int64_t* slot_mapping;
+};
+
+static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t,
+                       int64_t out_stride_h, const void* k_cache, const void* v_cache, int64_t stride_block,
+                       int64_t stride_slot, int64_t stride_head, int64_t num_blocks, const int32_t* block_table,
+                       int64_t block_table_stride, const int32_t* seq_lens, int32_t num_seqs, int32_t num_q_heads,
+                       int32_t num_kv_heads, int32_t head_dim, int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
+                       float sm_scale, const float* k_scale, const float* v_scale, int32_t scale_stride,
+                       const void* plan, int32_t num_ctas, void* workspace, size_t workspace_bytes,
+                       float* lse_out, const int32_t* row_map, int32_t fresh_tokens, int32_t flags, void* stream,
+                       const NewTokens* nw) {
   if (num_seqs == 0) return B200ATTN_OK;
   if (!q || !out || !k_cache || !v_cache || !block_table || !seq_lens || !plan || !workspace) {
     set_error("decode: null pointer argument");
@@ -674,10 +684,35 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stri
   p.cluster = 1;
   p.debug = option_debug();
   p.dbg = option_debug_buffer();
+  p.new_key = nullptr; p.new_value = nullptr; p.slot_mapping = nullptr;
+  p.nk_stride_t = p.nk_stride_h = p.nv_stride_t = p.nv_stride_h = 0;
+  p.kc_base = nullptr; p.vc_base = nullptr;
+  p.c_stride_block = stride_block; p.c_stride_slot = stride_slot; p.c_stride_head = stride_head;
+  p.block_size = block_size;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool use_tc = fp8 && G <= 8 && option_tc();
+  if (nw != nullptr) {
+    // In-kernel write: the tcgen05 kernel, rows == tokens (no row_map: with several query tokens per request a later row
+    // reads what an earlier row's CTA writes).  Every other shape runs the KV-write kernel first -- same result, two launches.
+    if (use_tc && row_map == nullptr && option_fused_write()) {
+      p.new_key = nw->key; p.new_value = nw->value; p.slot_mapping = nw->slot_mapping;
+      p.nk_stride_t = nw->key_stride_t; p.nk_stride_h = nw->key_stride_h;
+      p.nv_stride_t = nw->value_stride_t; p.nv_stride_h = nw->value_stride_h;
+      p.kc_base = reinterpret_cast<uint8_t*>(const_cast<void*>(k_cache));
+      p.vc_base = reinterpret_cast<uint8_t*>(const_cast<void*>(v_cache));
+      if (p.fresh == 0) p.fresh = 1;   // the row's last position is written by this launch: never read it before the wait
+    } else {
+      rc = b200attn_kv_write(nw->key, nw->value, nw->key_stride_t, nw->key_stride_h, nw->value_stride_t, nw->value_stride_h,
+                             const_cast<void*>(k_cache), const_cast<void*>(v_cache), stride_block, stride_slot, stride_head,
+                             nw->slot_mapping, num_seqs, num_kv_heads, head_dim, block_size, q_dtype, kv_dtype, k_scale, v_scale,
+                             scale_stride, stream);
+      if (rc) return rc;
+      if (p.fresh == 0) p.fresh = 1;
+    }
+  }
   // fp8 KV with at most 8 query heads per kv head: both GEMMs on tcgen05 (decode_tc.cu); everything else: HMMA consumers
-  if (fp8 && G <= 8 && option_tc()) return launch_decode_tc(tk, tv, p, num_ctas, q_dtype, st);
+  if (use_tc) return launch_decode_tc(tk, tv, p, num_ctas, q_dtype, st);
   const int nt = G > 8 ? 2 : 1;
 #define B200_LAUNCH(KVT, QDT)                                                       \
   (nt == 2 ? launch_decode<KVT, QDT, 2>(tk, tv, p, num_ctas, st) : launch_decode<KVT, QDT, 1>(tk, tv, p, num_ctas, st))
@@ -685,4 +720,46 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stri
   if (kv_dtype == B200ATTN_BF16) return B200_LAUNCH(B200ATTN_BF16, B200ATTN_BF16);
   return B200_LAUNCH(B200ATTN_FP16, B200ATTN_FP16);
 #undef B200_LAUNCH
+}
+
+extern "C" int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t,
+                               int64_t out_stride_h, const void* k_cache, const void* v_cache, int64_t stride_block,
+                               int64_t stride_slot, int64_t stride_head, int64_t num_blocks, const int32_t* block_table,
+                               int64_t block_table_stride, const int32_t* seq_lens, int32_t num_seqs, int32_t num_q_heads,
+                               int32_t num_kv_heads, int32_t head_dim, int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
+                               float sm_scale, const float* k_scale, const float* v_scale, int32_t scale_stride,
+                               const void* plan, int32_t num_ctas, void* workspace, size_t workspace_bytes,
+                               float* lse_out, const int32_t* row_map, int32_t fresh_tokens, int32_t flags, void* stream) {
+  return decode_impl(q, q_stride_t, q_stride_h, out, out_stride_t, out_stride_h, k_cache, v_cache, stride_block, stride_slot,
+                     stride_head, num_blocks, block_table, block_table_stride, seq_lens, num_seqs, num_q_heads, num_kv_heads,
+                     head_dim, block_size, q_dtype, kv_dtype, sm_scale, k_scale, v_scale, scale_stride, plan, num_ctas, workspace,
+                     workspace_bytes, lse_out, row_map, fresh_tokens, flags, stream, nullptr);
+}
+
+extern "C" int b200attn_decode_kv_write(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t,
+                                        int64_t out_stride_h, const void* key, const void* value, int64_t key_stride_t,
+                                        int64_t key_stride_h, int64_t value_stride_t, int64_t value_stride_h,
+                                        const int64_t* slot_mapping, void* k_cache, void* v_cache, int64_t stride_block,
+                                        int64_t stride_slot, int64_t stride_head, int64_t num_blocks, const int32_t* block_table,
+                                        int64_t block_table_stride, const int32_t* seq_lens, int32_t num_seqs,
+                                        int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                                        int32_t q_dtype, int32_t kv_dtype, float sm_scale, const float* k_scale,
+                                        const float* v_scale, int32_t scale_stride, const void* plan, int32_t num_ctas,
+                                        void* workspace, size_t workspace_bytes, float* lse_out, const int32_t* row_map,
+                                        int32_t fresh_tokens, int32_t flags, void* stream) {
+  if (num_seqs == 0) return B200ATTN_OK;
+  if (!key || !value || !slot_mapping) {
+    set_error("decode_kv_write: null key / value / slot_mapping");
+    return B200ATTN_EINVAL;
+  }
+  auto mis = [](const void* ptr, int64_t a) { return (reinterpret_cast<uintptr_t>(ptr) % a) != 0; };
+  if (mis(key, 16) || mis(value, 16) || (key_stride_t % 8) || (key_stride_h % 8) || (value_stride_t % 8) || (value_stride_h % 8)) {
+    set_error("decode_kv_write: key / value must be 16-byte aligned with strides that are multiples of 8 elements");
+    return B200ATTN_EINVAL;
+  }
+  NewTokens nw = {key, value, key_stride_t, key_stride_h, value_stride_t, value_stride_h, slot_mapping};
+  return decode_impl(q, q_stride_t, q_stride_h, out, out_stride_t, out_stride_h, k_cache, v_cache, stride_block, stride_slot,
+                     stride_head, num_blocks, block_table, block_table_stride, seq_lens, num_seqs, num_q_heads, num_kv_heads,
+                     head_dim, block_size, q_dtype, kv_dtype, sm_scale, k_scale, v_scale, scale_stride, plan, num_ctas, workspace,
+                     workspace_bytes, lse_out, row_map, fresh_tokens, flags, stream, &nw);
 }

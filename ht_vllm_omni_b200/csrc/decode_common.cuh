@@ -30,6 +30,17 @@ struct DecodeParams {
   int fused_merge;      // 1: the last CTA to finish a split (sequence, kv head) pair merges its partials in-kernel
   int cluster;          // thread-block cluster size of this launch (1: none); partials of a pair whose CTAs share a cluster
                         // are folded through distributed shared memory instead of the L2 workspace
+  // Fused KV write (pure-decode steps; b200attn_decode_kv_write): the CTA that streams the tile holding a row's LAST position
+  // first quantises and stores that row's new key / value (token index == row index) to the cache, then reads the tile.
+  // new_key == nullptr: the cache was written by an earlier kernel (b200attn_decode).
+  const void* new_key;
+  const void* new_value;
+  int64_t nk_stride_t, nk_stride_h, nv_stride_t, nv_stride_h;
+  const int64_t* slot_mapping;
+  uint8_t* kc_base;
+  uint8_t* vc_base;
+  int64_t c_stride_block, c_stride_slot, c_stride_head;   // elements (= bytes for the fp8 cache)
+  int block_size;
   unsigned long long* dbg;  // debug timeline buffer [grid][16] (globaltimer ns) or nullptr
   int debug;            // bit0: consumers skip the math (pure streaming ceiling); never set in production
 };

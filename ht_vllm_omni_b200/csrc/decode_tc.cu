@@ -270,6 +270,10 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
     int blk = 0, blk_next = 0;
     const int32_t* bt = nullptr;
     int kvh = 0;
+    bool nt_loaded = false, nt_stored = false;   // fused KV write: the row's new token is in registers / in the cache
+    int64_t nt_slot = -1;
+    uint4 nt_raw = make_uint4(0u, 0u, 0u, 0u);
+    float nt_scale = 1.f;
     if (kDbg && lane == 0) dbg_stamp(p, 8);
     while (cur.next_tile(p)) {
       const int tok0 = cur.tok0();
@@ -295,6 +299,48 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       const bool early_ok = !waited && early_left > 0 && tok0 + kTcTile <= cur.seg_L - p.fresh;
       if (!early_ok && !waited) { pdl_wait(); waited = true; }
       if (early_ok) --early_left;
+      // ---- fused KV write: the piece that ends its row owns the row's new token.  Lanes 0-15 carry 8 key elements each,
+      // lanes 16-31 the value's.  The loads are requested at the first tile after the wait above (key / value come from the
+      // kernel before us), the bytes go to the cache one tile later -- mid-stream, where the ring hides the producer's stall --
+      // or at the latest right before the TMA of the tile that holds position L - 1 reads them back
+      // (generic-proxy store -> fence.proxy.async -> async-proxy load, same warp).
+      if (p.new_key != nullptr && cur.seg_end == cur.seg_L) {
+        if (cur.first()) { nt_loaded = false; nt_stored = false; }
+        bool just_loaded = false;
+        if (!nt_loaded && waited) {
+          const int hl = lane & 15;
+          const uint16_t* src = lane < 16
+              ? reinterpret_cast<const uint16_t*>(p.new_key) + (int64_t)cur.seg_s * p.nk_stride_t + (int64_t)kvh * p.nk_stride_h + hl * 8
+              : reinterpret_cast<const uint16_t*>(p.new_value) + (int64_t)cur.seg_s * p.nv_stride_t + (int64_t)kvh * p.nv_stride_h + hl * 8;
+          nt_slot = __ldg(p.slot_mapping + cur.seg_s);
+          nt_raw = ldg_nc_v4(src);
+          nt_scale = __ldg((lane < 16 ? p.k_scale : p.v_scale) + (int64_t)kvh * p.scale_stride);
+          nt_loaded = true;
+          just_loaded = true;
+        }
+        if (nt_loaded && !nt_stored && (!just_loaded || cur.last())) {
+          if (nt_slot >= 0) {
+            float f[8];
+            f[0] = q_to_float<QDT>(nt_raw.x & 0xffff); f[1] = q_to_float<QDT>(nt_raw.x >> 16);
+            f[2] = q_to_float<QDT>(nt_raw.y & 0xffff); f[3] = q_to_float<QDT>(nt_raw.y >> 16);
+            f[4] = q_to_float<QDT>(nt_raw.z & 0xffff); f[5] = q_to_float<QDT>(nt_raw.z >> 16);
+            f[6] = q_to_float<QDT>(nt_raw.w & 0xffff); f[7] = q_to_float<QDT>(nt_raw.w >> 16);
+            // x / scale in fp32 with IEEE rounding, then round-to-nearest-even + saturate-to-finite: kv_write.cu's arithmetic
+            const uint32_t w0 = f32x2_to_e4m3x2(__fdiv_rn(f[0], nt_scale), __fdiv_rn(f[1], nt_scale)) |
+                                (f32x2_to_e4m3x2(__fdiv_rn(f[2], nt_scale), __fdiv_rn(f[3], nt_scale)) << 16);
+            const uint32_t w1 = f32x2_to_e4m3x2(__fdiv_rn(f[4], nt_scale), __fdiv_rn(f[5], nt_scale)) |
+                                (f32x2_to_e4m3x2(__fdiv_rn(f[6], nt_scale), __fdiv_rn(f[7], nt_scale)) << 16);
+            const int64_t nblk = nt_slot / p.block_size, noff = nt_slot - nblk * p.block_size;
+            uint8_t* dst = (lane < 16 ? p.kc_base : p.vc_base) + nblk * p.c_stride_block + noff * p.c_stride_slot +
+                           (int64_t)kvh * p.c_stride_head + (lane & 15) * 8;
+            asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(dst), "r"(w0), "r"(w1) : "memory");
+          }
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+          __syncwarp();
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+          nt_stored = true;
+        }
+      }
       const int nbox = (cur.valid() + kChunkTokens - 1) / kChunkTokens;
       const uint32_t st = it % kTcStages, par = ((it / kTcStages) & 1) ^ 1;
       const int c = lane & 7;

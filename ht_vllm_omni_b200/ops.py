@@ -203,6 +203,31 @@ def launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, pla
         _stream(query)), "b200attn_decode")
 
 
+def launch_split_decode_kv_write(query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out, plan, workspace,
+                                 k_scale, v_scale, sm_scale, num_ctas, lse=None, row_map=None, fresh_tokens=1,
+                                 fused_merge=False) -> None:
+    """b200attn_decode_kv_write: the rows' new tokens are written to the cache by the decode launch itself (FP8 cache, <= 8
+    query heads per kv head, rows == tokens) or by a KV-write launch issued from the same call (every other shape)."""
+    (sb, ss, sh), kvdt, sstride = _decode_args(query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale)
+    n = seq_lens.shape[0]
+    if key.dim() != 3 or value.shape != key.shape or key.stride(2) != 1 or value.stride(2) != 1 or key.dtype != query.dtype \
+            or value.dtype != query.dtype or key.shape[0] < n:
+        raise B200AttnError("key/value must be [rows, Hkv, D] of the query dtype with contiguous head_dim")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous() or slot_mapping.shape[0] < n:
+        raise B200AttnError("slot_mapping must be contiguous int64 covering every row")
+    if row_map is not None and (row_map.dtype != torch.int32 or not row_map.is_contiguous() or row_map.shape[0] != n):
+        raise B200AttnError("row_map must be contiguous int32 [num_rows]")
+    check(load_library().b200attn_decode_kv_write(
+        query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1),
+        key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1), value.stride(0), value.stride(1), slot_mapping.data_ptr(),
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, k_cache.shape[0], block_table.data_ptr(), block_table.stride(0),
+        seq_lens.data_ptr(), n, query.shape[1], k_cache.shape[2], query.shape[2], k_cache.shape[1],
+        _dt(query), kvdt, float(sm_scale), k_scale.data_ptr(), v_scale.data_ptr(), sstride, plan.data_ptr(), num_ctas,
+        workspace.data_ptr(), workspace.numel() * 4, lse.data_ptr() if lse is not None else None,
+        row_map.data_ptr() if row_map is not None else None, int(fresh_tokens), DECODE_FUSED_MERGE if fused_merge else 0,
+        _stream(query)), "b200attn_decode_kv_write")
+
+
 def launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse=None) -> None:
     """Kernel 3 only (b200attn_merge); must follow launch_split_decode on the same stream."""
     kvdt = _dt(k_cache)
@@ -243,6 +268,35 @@ def paged_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tens
 @paged_decode.register_fake
 def _(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale, num_ctas, lse,
       row_map, fresh_tokens=-1, fused_merge=True) -> None:
+    return None
+
+
+@torch.library.custom_op("b200attn::paged_decode_kv_write", mutates_args=("k_cache", "v_cache", "out", "plan", "workspace", "lse"),
+                         device_types="cuda")
+def paged_decode_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, slot_mapping: torch.Tensor,
+                          k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor, seq_lens: torch.Tensor,
+                          out: torch.Tensor, plan: torch.Tensor, workspace: torch.Tensor, k_scale: torch.Tensor,
+                          v_scale: torch.Tensor, sm_scale: float, num_ctas: int, lse: torch.Tensor, row_map: torch.Tensor,
+                          fresh_tokens: int = 1, fused_merge: bool = True) -> None:
+    """KV write + paged decode of a PURE-DECODE step in one call (a backend with forward_includes_kv_cache_update = True):
+    key[b] / value[b] go to slot_mapping[b] exactly as torch.ops.b200attn.kv_write stores them, and row b attends to its
+    seq_lens[b] positions including that token.  Other arguments as paged_decode."""
+    _require_cuda(query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out, plan, workspace)
+    if seq_lens.shape[0] == 0:
+        return
+    lse = lse if lse.numel() > 0 else None
+    row_map = row_map if row_map.numel() > 0 else None
+    if fused_merge and seq_lens.shape[0] * k_cache.shape[2] * 8 < num_ctas:
+        fused_merge = False
+    launch_split_decode_kv_write(query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out, plan, workspace,
+                                 k_scale, v_scale, sm_scale, num_ctas, lse, row_map, fresh_tokens, fused_merge)
+    if not fused_merge:
+        launch_merge(k_cache, seq_lens, out, plan, workspace, v_scale, num_ctas, lse)
+
+
+@paged_decode_kv_write.register_fake
+def _(query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
+      num_ctas, lse, row_map, fresh_tokens=1, fused_merge=True) -> None:
     return None
 
 
@@ -382,6 +436,13 @@ class DecodeWorkspace:
         self.grid = self.grid_for(seq_lens.shape[0], num_q_heads, num_kv_heads)
         torch.ops.b200attn.decode_plan(seq_lens, self.plan, num_q_heads, num_kv_heads, self.grid, block_table, block_size,
                                        self._no_map if row_map is None else row_map)
+
+    def decode_kv_write(self, query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale,
+                        sm_scale, lse=None, row_map=None, fresh_tokens: int = 1, fused_merge: bool = True) -> None:
+        torch.ops.b200attn.paged_decode_kv_write(query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out,
+                                                 self.plan, self.workspace, k_scale, v_scale, sm_scale, self.grid,
+                                                 self._no_lse if lse is None else lse,
+                                                 self._no_map if row_map is None else row_map, fresh_tokens, fused_merge)
 
     def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None,
                row_map=None, fresh_tokens: int = -1, fused_merge: bool = True) -> None:

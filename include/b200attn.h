@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 4
+#define B200ATTN_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -184,6 +184,40 @@ B200ATTN_API int b200attn_decode(const void* q, int64_t q_stride_t, int64_t q_st
                     void* stream);
 
 /*
+ * Kernels 1 + 2 in one call for a PURE-DECODE step (one query token per row): the new token of row b -- key[b], value[b],
+ * destined for slot_mapping[b] (< 0: not written) -- is quantised and stored to the cache with b200attn_kv_write's
+ * arithmetic (bit-identical bytes), and attention then runs over seq_lens[b] positions that include it.
+ * Replaces: do_kv_cache_update + forward of a backend that declares `forward_includes_kv_cache_update = True`
+ *   ($VLLM/v1/attention/backend.py:66; the runner then hands forward() the UNPADDED slot_mapping,
+ *   vllm_omni/worker/gpu_ar_model_runner.py:231-244), i.e. reshape_and_cache_flash followed by the decode branch.
+ * With an FP8 cache, <= 8 query heads per kv head and no row_map, the write happens INSIDE the decode kernel: the CTA that
+ * streams the tile holding a row's last position stores the row's new token right before its TMA reads the tile back
+ * (generic-proxy store, fence.proxy.async, async-proxy load) -- one launch per layer instead of two and no kernel
+ * boundary between the write and the read.  Every other shape (16-bit cache, > 8 heads per kv head, row_map != NULL, or
+ * option "fused_write" = 0) runs the KV-write kernel and then the decode kernel from this one call: same bytes, same output.
+ * key / value dtype = q_dtype.  All other arguments as b200attn_decode.
+ */
+B200ATTN_API int b200attn_decode_kv_write(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+                    void* out, int64_t out_stride_t, int64_t out_stride_h,
+                    const void* key, const void* value,
+                    int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t, int64_t value_stride_h,
+                    const int64_t* slot_mapping,
+                    void* k_cache, void* v_cache,
+                    int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                    int64_t num_blocks,
+                    const int32_t* block_table, int64_t block_table_stride,
+                    const int32_t* seq_lens, int32_t num_seqs,
+                    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                    int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
+                    float sm_scale, const float* k_scale, const float* v_scale,
+                    int32_t scale_stride,
+                    const void* plan, int32_t num_ctas,
+                    void* workspace, size_t workspace_bytes,
+                    float* lse_out /* nullable */,
+                    const int32_t* row_map /* nullable */, int32_t fresh_tokens, int32_t flags,
+                    void* stream);
+
+/*
  * Kernel 3 — merge of split-KV partials (online-softmax reduction with warp shuffles).
  * Replaces: reduce_segments ($VLLM/v1/attention/ops/triton_unified_attention.py:645-733) and the
  *   in-kernel reduction of the TRT-LLM-gen "MultiCtasKv" cubins.
@@ -275,7 +309,8 @@ B200ATTN_API int b200attn_kv_gather(const void* const* k_planes, const void* con
 /*
  * Runtime knobs (host, process-wide): "pdl" (programmatic dependent launch, default 1), "tc" (tcgen05 consumer for
  * fp8 KV with group size <= 8, default 1), "cluster" (thread-block cluster size of that kernel: partials of a split
- * pair whose CTAs share a cluster are merged through distributed shared memory; default 2, 1 = off).
+ * pair whose CTAs share a cluster are merged through distributed shared memory; default 2, 1 = off), "fused_write"
+ * (b200attn_decode_kv_write stores the new token inside the decode kernel when the shape allows, default 1).
  * Returns the previous value or B200ATTN_EINVAL for an unknown name.
  */
 B200ATTN_API int b200attn_set_option(const char* name, int32_t value);

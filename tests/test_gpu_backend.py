@@ -31,12 +31,16 @@ def _alloc_like_vllm(be, nb, bs, Hkv, D, kv_cache_dtype, torch_dtype):
     return raw.view(torch_dtype).view(phys).permute(*inv)
 
 
+@pytest.mark.parametrize("contract", ["forward_writes_kv", "separate_kv_update"])
 @pytest.mark.parametrize("kv_cache_dtype", ["fp8", "auto"])
 @pytest.mark.parametrize("q_lens", [[1, 1, 1, 1], [1, 3, 2, 7]], ids=["pure_decode", "mixed_multi_token_rows"])
-def test_backend_step_matches_oracle(kv_cache_dtype, q_lens):
+def test_backend_step_matches_oracle(kv_cache_dtype, q_lens, contract, monkeypatch):
+    """Both contracts vLLM knows (attention.py:493): forward() owns the KV write (the default: on a pure-decode step the
+    store happens inside the decode launch), or unified_kv_cache_update -> do_kv_cache_update precedes forward()."""
     from ht_vllm_omni_b200 import backend as B
 
     be = B.B200PagedAttentionBackend
+    monkeypatch.setattr(be, "forward_includes_kv_cache_update", contract == "forward_writes_kv")
     Hq, Hkv, D, bs = 16, 2, 128, 16
     fp8 = kv_cache_dtype == "fp8"
     ctx = np.array([300, 40, 0, 1000], np.int32)              # tokens already in the cache
@@ -85,7 +89,8 @@ def test_backend_step_matches_oracle(kv_cache_dtype, q_lens):
     spec = types.SimpleNamespace(block_size=bs, dtype=cache_dt)
     builder = be.get_builder_cls()(spec, ["layer.0"], _cfg(Hq, Hkv, D, 64), torch.device("cuda"))
     md = builder.build(0, cm)
-    impl.do_kv_cache_update(layer, d_k, d_v, kv_cache, cm.slot_mapping)
+    if not be.forward_includes_kv_cache_update:
+        impl.do_kv_cache_update(layer, d_k, d_v, kv_cache, cm.slot_mapping)
     output = torch.full((T + pad, Hq * D), 7.0, dtype=torch.bfloat16, device="cuda")
     ret = impl.forward(layer, d_q, d_k, d_v, kv_cache, md, output)
     torch.cuda.synchronize()
@@ -106,12 +111,15 @@ def test_backend_step_matches_oracle(kv_cache_dtype, q_lens):
     assert np.all(err <= tol + np.maximum(np.abs(ref), 2.0 ** -14) * 2.0 ** -7), float(err.max())
 
 
-def test_backend_under_cuda_graph_replay_with_changing_seq_lens():
+@pytest.mark.parametrize("contract", ["forward_writes_kv", "separate_kv_update"])
+def test_backend_under_cuda_graph_replay_with_changing_seq_lens(contract, monkeypatch):
     """FULL-graph decode: capture once at a padded batch, replay after the runner updates seq_lens / block_table /
-    slot_mapping IN PLACE (the plan kernel re-reads them on the device; nothing is baked in at capture)."""
+    slot_mapping IN PLACE (the plan kernel re-reads them on the device; nothing is baked in at capture).  Under the
+    forward-writes contract the captured launch is the decode that also stores the tokens (slots -1 here: padding)."""
     from ht_vllm_omni_b200 import backend as B
 
     be = B.B200PagedAttentionBackend
+    monkeypatch.setattr(be, "forward_includes_kv_cache_update", contract == "forward_writes_kv")
     Hq, Hkv, D, bs, Bp = 16, 2, 128, 16, 8
     impl = be.get_impl_cls()(Hq, D, D ** -0.5, Hkv, None, None, "fp8")
     layer = types.SimpleNamespace(_k_scale=torch.tensor([0.02], device="cuda"), _v_scale=torch.tensor([0.02], device="cuda"))
@@ -134,7 +142,8 @@ def test_backend_under_cuda_graph_replay_with_changing_seq_lens():
 
     def step():
         md = builder.build_for_cudagraph_capture(cm)
-        impl.do_kv_cache_update(layer, kvn, kvn, kv_cache, d_slots)     # all slots -1: writes nothing
+        if not be.forward_includes_kv_cache_update:
+            impl.do_kv_cache_update(layer, kvn, kvn, kv_cache, d_slots)     # all slots -1: writes nothing
         impl.forward(layer, q, kvn, kvn, kv_cache, md, out)
 
     s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
@@ -157,8 +166,9 @@ def test_backend_under_cuda_graph_replay_with_changing_seq_lens():
         assert np.all(err <= 1e-2 + np.maximum(np.abs(ref[live]), 2.0 ** -14) * 2.0 ** -7), float(err.max())
 
 
-def test_full_graph_captures_forward_only_and_build_runs_eagerly_before_each_replay():
-    """vLLM's FULL-cudagraph flow: `build()` runs eagerly before every replay, only the layer hooks are inside
+def test_full_graph_captures_forward_only_and_build_runs_eagerly_before_each_replay(monkeypatch):
+    """Two-op contract (B200ATTN_SEPARATE_KV_UPDATE=1), the one under which the builder declares AttentionCGSupport.ALWAYS.
+    vLLM's FULL-cudagraph flow: `build()` runs eagerly before every replay, only the layer hooks are inside
     the graph.  One graph per token count serves BOTH a batch with multi-token requests and a pure-decode batch of the same
     size, so the captured kernels must read their row lengths / row map from buffers that do not depend on which of the two
     the batch is.  Capture on a mixed batch (3 requests, q_lens 2+1+1), replay on a pure-decode batch (4 requests), then on
@@ -166,6 +176,8 @@ def test_full_graph_captures_forward_only_and_build_runs_eagerly_before_each_rep
     from ht_vllm_omni_b200 import backend as B
 
     be = B.B200PagedAttentionBackend
+    monkeypatch.setattr(be, "forward_includes_kv_cache_update", False)
+    assert be.get_builder_cls().get_cudagraph_support(None, None) == vb.AttentionCGSupport.ALWAYS
     Hq, Hkv, D, bs, T, R = 16, 2, 128, 16, 4, 4
     impl = be.get_impl_cls()(Hq, D, D ** -0.5, Hkv, None, None, "fp8")
     layer = types.SimpleNamespace(_k_scale=torch.tensor([0.02], device="cuda"), _v_scale=torch.tensor([0.02], device="cuda"))

@@ -182,6 +182,30 @@ def time_vllm_kv_write(caches, kn, vn, slots, k_scale_t, v_scale_t, nbytes):
         return {"error": f"{type(e).__name__}: {str(e)[:300]}"}
 
 
+def time_vllm_query_quant(q):
+    """The static per-tensor FP8 quantisation of the query that vLLM's Attention.forward issues in front of an FP8-query
+    TRT-LLM-gen call (`query_quant`, $VLLM/model_executor/layers/attention/attention.py:461-471; under torch.compile it can
+    fuse into the producer of q, eager / custom-op mode launches it as timed here).  q [NL, B, Hq, D] bf16."""
+    try:
+        import vllm._custom_ops as cops
+    except Exception as e:  # noqa: BLE001
+        return {"error": f"import vllm._custom_ops: {type(e).__name__}: {e}"}
+    try:
+        NL, B, Hq, D = q.shape
+        scale = torch.full((1,), float(q.float().abs().max()) / 448.0, dtype=torch.float32, device=q.device)
+        q2 = q.reshape(NL, B, Hq * D)
+
+        def body():
+            for l in range(NL):
+                cops.scaled_fp8_quant(q2[l], scale)
+
+        us, graphed = _graph_time(body, NL)
+        return _res(us, graphed, B * Hq * D * 3)
+    except Exception as e:  # noqa: BLE001
+        torch.cuda.synchronize()
+        return {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+
+
 def max_abs_vs(ours: torch.Tensor, other) -> float | None:
     if not isinstance(other, dict) or "out" not in other:
         return None
@@ -209,6 +233,8 @@ def compare_all(phys_caches, q, bt, lens, sm_scale, k_scale_t, v_scale_t, dec_by
         res["fa4_flash_attn_varlen"] = time_fa4(planes, q, bt, lens, max_len, sm_scale, dec_bytes)
     if "kv_write" in arms and kn is not None:
         res["vllm_reshape_and_cache_flash"] = time_vllm_kv_write(planes, kn, vn, slots, k_scale_t, v_scale_t, wr_bytes)
+    if "flashinfer_q8" in arms and fp8:
+        res["vllm_query_fp8_quant"] = time_vllm_query_quant(q)
     for k, v in res.items():
         if ours_out is not None:
             m = max_abs_vs(ours_out, v)
