@@ -104,3 +104,53 @@ def test_install_layer_scales_per_tensor_in_place():
     S.install_layer_scales(layer, torch.tensor([0.3]), torch.tensor([0.6]))
     assert layer._k_scale.data_ptr() == before and float(layer._k_scale) == pytest.approx(0.3)
     assert layer._v_scale_float == pytest.approx(0.6)
+
+
+def test_plugin_installs_per_head_method_into_the_reference_quant_routing(monkeypatch):
+    """plugin.register() wraps ComponentQuantizationConfig.get_quant_method (vllm_omni/quantization/component_config.py:53-57)
+    without editing the reference: Attention layers served by this backend with an FP8 cache get PerHeadKVCacheMethod where
+    vLLM would have handed out its per-tensor BaseKVCacheMethod; everything else is passed through untouched.  vllm_omni is
+    not importable in this image, so a stand-in module with the reference's class shape is installed."""
+    import sys
+    import types
+
+    from vllm.model_executor.layers.quantization.kv_cache import BaseKVCacheMethod
+
+    from ht_vllm_omni_b200 import backend as BK
+    from ht_vllm_omni_b200 import plugin
+
+    class ComponentQuantizationConfig:           # shape of the reference class: resolve(prefix) -> config -> get_quant_method
+        def __init__(self, method):
+            self.method = method
+
+        def get_quant_method(self, layer, prefix):
+            return self.method
+
+    mod = types.ModuleType("vllm_omni.quantization.component_config")
+    mod.ComponentQuantizationConfig = ComponentQuantizationConfig
+    for name in ("vllm_omni", "vllm_omni.quantization"):
+        monkeypatch.setitem(sys.modules, name, types.ModuleType(name))
+    monkeypatch.setitem(sys.modules, "vllm_omni.quantization.component_config", mod)
+
+    assert plugin.install_per_head_kv_scales() is True
+    assert plugin.install_per_head_kv_scales() is True            # idempotent: wrapped once
+    assert ComponentQuantizationConfig.get_quant_method.__wrapped__.__name__ == "get_quant_method"
+    assert not hasattr(ComponentQuantizationConfig.get_quant_method.__wrapped__, "__wrapped__")
+
+    per_tensor = BaseKVCacheMethod.__new__(BaseKVCacheMethod)
+    ours = Layer("fp8"); ours.attn_backend = BK.B200PagedAttentionBackend; ours.num_kv_heads = 4
+    m = ComponentQuantizationConfig(per_tensor).get_quant_method(ours, "talker.layers.0.self_attn.attn")
+    assert isinstance(m, S.PerHeadKVCacheMethod) and m.num_kv_heads == 4 and m.total_num_kv_heads == 4
+    # ... and it loads a per-head checkpoint vector onto the layer
+    m.create_weights(ours)
+    ours.k_scale.data.copy_(torch.tensor([0.1, 0.2, 0.3, 0.4])); ours.v_scale.data.copy_(torch.tensor([0.5, 0.6, 0.7, 0.8]))
+    m.process_weights_after_loading(ours)
+    assert ours._k_scale.tolist() == pytest.approx([0.1, 0.2, 0.3, 0.4]) and ours._v_scale.tolist() == pytest.approx([0.5, 0.6, 0.7, 0.8])
+
+    other_backend = Layer("fp8"); other_backend.attn_backend = type("Other", (), {}); other_backend.num_kv_heads = 4
+    assert ComponentQuantizationConfig(per_tensor).get_quant_method(other_backend, "x") is per_tensor
+    bf16 = Layer("auto"); bf16.attn_backend = BK.B200PagedAttentionBackend; bf16.num_kv_heads = 4
+    assert ComponentQuantizationConfig(per_tensor).get_quant_method(bf16, "x") is per_tensor
+    assert ComponentQuantizationConfig(None).get_quant_method(ours, "x") is None          # no config for the prefix: unchanged
+    linear_method = object()
+    assert ComponentQuantizationConfig(linear_method).get_quant_method(ours, "x") is linear_method
