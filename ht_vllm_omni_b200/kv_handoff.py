@@ -78,14 +78,49 @@ def gather_request_kv(block_ids: Sequence[int], seq_len: int, kv_caches: Sequenc
     return key_cache, value_cache
 
 
+def kv_scale_metadata(kv_scales: Sequence[Any]) -> dict[str, list]:
+    """FP8 caches travel as raw e4m3 bytes; the receiving stage needs the scales to read them (value = byte * scale[head]).
+    `kv_scales`: per layer a (k_scale, v_scale) pair -- the attention layer's `_k_scale` / `_v_scale` tensors (1 element =
+    per-tensor, Hkv elements = per-head) or floats -- or None for a layer without a cache.  Returns plain lists of floats per
+    layer (JSON / msgpack friendly, like the rest of the metadata), fetched with ONE device->host copy."""
+    flat, shape = [], []
+    for pair in kv_scales:
+        if pair is None:
+            shape.append(None)
+            continue
+        k, v = (torch.as_tensor(x, dtype=torch.float32).reshape(-1) for x in pair)
+        shape.append((k.numel(), v.numel()))
+        flat += [k, v]
+    if not flat:
+        return {"k_scale": [None] * len(shape), "v_scale": [None] * len(shape)}
+    dev = next((t.device for t in flat if t.is_cuda), flat[0].device)
+    host = torch.cat([t.to(dev) for t in flat]).cpu().tolist()
+    ks, vs, o = [], [], 0
+    for sh in shape:
+        if sh is None:
+            ks.append(None); vs.append(None)
+            continue
+        ks.append(host[o:o + sh[0]]); o += sh[0]
+        vs.append(host[o:o + sh[1]]); o += sh[1]
+    return {"k_scale": ks, "v_scale": vs}
+
+
 def extract_kv_cache(req_id: str, block_ids: list[int], seq_len: int, kv_caches: list, block_size: int, cache_dtype: str,
-                     custom_metadata: dict[str, Any] | None = None) -> dict | None:
+                     custom_metadata: dict[str, Any] | None = None, kv_scales: Sequence[Any] | None = None) -> dict | None:
     """Drop-in for `_extract_kv_cache`: the reference wraps the same fields in its KVCacheTransferData dataclass
-    (request_id, layer_blocks, block_ids, metadata); INTEGRATION.md shows the two-line change that makes it call this."""
+    (request_id, layer_blocks, block_ids, metadata); INTEGRATION.md shows the two-line change that makes it call this.
+    `kv_scales` (one (k_scale, v_scale) per layer, see `kv_scale_metadata`) adds `metadata["kv_scales"]` so an FP8 cache's raw
+    bytes can be dequantised downstream ("raw bytes + scales in metadata"); the reference's own fields and
+    their meaning are unchanged, and callers that pass nothing get exactly the reference's metadata."""
     got = gather_request_kv(block_ids, seq_len, kv_caches)
     if got is None:
         return None
     key_cache, value_cache = got
+    meta = {"block_size": block_size, "num_layers": len(kv_caches), "dtype": str(cache_dtype), "seq_len": seq_len}
+    if kv_scales is not None:
+        if len(kv_scales) != len(kv_caches):
+            raise B200AttnError(f"kv_scales must have one entry per layer ({len(kv_scales)} vs {len(kv_caches)})")
+        meta["kv_scales"] = kv_scale_metadata(kv_scales)
+    meta.update(custom_metadata or {})
     return {"request_id": req_id, "layer_blocks": {"key_cache": key_cache, "value_cache": value_cache}, "block_ids": block_ids,
-            "metadata": {"block_size": block_size, "num_layers": len(kv_caches), "dtype": str(cache_dtype), "seq_len": seq_len,
-                         **(custom_metadata or {})}}
+            "metadata": meta}

@@ -92,3 +92,41 @@ def test_gather_from_hnd_backend_cache_matches_oracle(kv):
         v = got[1][l].numpy() if kv == "fp8" else got[1][l].view(torch.int16).numpy()
         assert k.shape == (seq_len, H, D)
         assert np.array_equal(k, ref[0]) and np.array_equal(v, ref[1])
+
+
+def test_kv_scale_metadata_is_plain_lists_per_layer():
+    """`metadata["kv_scales"]`: what the receiving stage needs to read the raw e4m3 bytes (value = byte * scale[head])."""
+    from ht_vllm_omni_b200 import kv_handoff as H
+
+    m = H.kv_scale_metadata([(torch.tensor([0.5]), torch.tensor([0.25])), None, (torch.tensor([0.1, 0.2]), torch.tensor([0.3, 0.4])), (1.0, 2.0)])
+    assert m["k_scale"] == [[0.5], None, pytest.approx([0.1, 0.2]), [1.0]]
+    assert m["v_scale"] == [[0.25], None, pytest.approx([0.3, 0.4]), [2.0]]
+    assert H.kv_scale_metadata([None]) == {"k_scale": [None], "v_scale": [None]}
+
+
+@pytest.mark.gpu
+def test_extract_carries_fp8_scales_and_dequantises_to_the_written_values():
+    """Hand-off of an FP8 cache: raw bytes + per-head scales in the metadata reproduce, on the receiving side, exactly the
+    values the oracle's write produced (e4m3_decode(byte) * scale[head])."""
+    from ht_vllm_omni_b200 import kv_handoff as H
+
+    rng = np.random.default_rng(5)
+    nb, bs, Hkv, D, L = 12, 16, 2, 128, 3
+    phys = [torch.from_numpy(rng.integers(0, 0x78, size=(nb, 2, Hkv, bs, D), dtype=np.uint8)).cuda() for _ in range(L)]
+    caches = [p.permute(0, 1, 3, 2, 4) for p in phys]
+    scales = [(torch.tensor([0.01 * (l + 1), 0.02 * (l + 1)], device="cuda"), torch.tensor([0.03, 0.04], device="cuda")) for l in range(L)]
+    got = H.extract_kv_cache("r", [3, 9, 1], 40, caches, bs, "fp8", {"note": "x"}, kv_scales=scales)
+    md = got["metadata"]
+    assert md["note"] == "x" and md["seq_len"] == 40 and md["dtype"] == "fp8" and md["num_layers"] == L
+    for l in range(L):
+        ks = np.asarray(md["kv_scales"]["k_scale"][l], np.float32); vs = np.asarray(md["kv_scales"]["v_scale"][l], np.float32)
+        assert np.allclose(ks, [0.01 * (l + 1), 0.02 * (l + 1)]) and np.allclose(vs, [0.03, 0.04])
+        c = caches[l].cpu().numpy()
+        k_ref, _ = O.kv_extract_ref([3, 9, 1], 40, c[:, 0], c[:, 1])
+        k_bytes = got["layer_blocks"]["key_cache"][l].numpy()
+        assert np.array_equal(k_bytes, k_ref)
+        deq = O.e4m3_decode(k_bytes) * ks[None, :, None]
+        assert np.array_equal(deq, O.e4m3_decode(k_ref) * ks[None, :, None])
+    # without kv_scales the metadata is exactly the reference's
+    plain = H.extract_kv_cache("r", [3, 9, 1], 40, caches, bs, "fp8")
+    assert set(plain["metadata"]) == {"block_size", "num_layers", "dtype", "seq_len"}
