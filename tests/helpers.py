@@ -32,6 +32,7 @@ class Case:
         self.lens = np.asarray(lens, dtype=np.int32)
         self.B, self.Hq, self.Hkv, self.D, self.bs = len(lens), Hq, Hkv, D, bs
         self.kv, self.act, self.fp8 = kv, act, kv == "fp8"
+        self.dist = dist
         self.device = device
         g = torch.Generator().manual_seed(1234 + seed)
         self.bt_np, self.nb = O.make_block_table(self.lens, bs, seed=99 + seed, spare=spare)

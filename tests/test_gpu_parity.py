@@ -2,9 +2,18 @@
 oracle on the same seeded inputs, plus the committed golden vectors produced by vLLM's own kernels.
 
 Tolerances (BASELINE.json north_star): cache bytes bit-exact; attention max-abs 2e-3 (16-bit KV) / 1e-2 (FP8 KV).
-The kernel's output is rounded to bf16/fp16, so the comparison allows, on top of the stated tolerance, ONE unit in
-the last place of the output dtype at the reference's magnitude (a value of 0.9 in bf16 cannot be represented to
-better than 3.9e-3): `|got - ref| <= TOL + ulp(ref)`.  That allowance is spelled out in `assert_close`."""
+The kernel's output is rounded to bf16/fp16, which by itself moves a value of magnitude m by up to half a unit in the
+last place (m * 2^-8 for bf16: 1.9e-3 at m = 0.9).  `assert_close` therefore checks
+  * |got - ref| <= TOL                      wherever |ref| < 0.25 (the output rounding is below TOL/2 there): the bare tolerance;
+  * |got - ref| <= TOL + 1/2 ulp(ref)        against the fp64 oracle (an unrounded reference);
+  * |got - ref| <= TOL + 1 ulp(ref)          against a reference that is itself rounded to the output dtype (the reference-style
+                                             oracle, vLLM's goldens): two roundings can land one ulp apart.
+Only the heavy-tailed saturation case scales TOL (attention is a convex combination of V rows; its |V| reaches 30+).
+The largest error each test row observed is recorded in gpurun_out/parity_max_abs.json (and printed with -s)."""
+import atexit
+import json
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -15,19 +24,40 @@ pytestmark = pytest.mark.gpu
 
 TOL = {"fp8": 1e-2, "bf16": 2e-3, "fp16": 2e-3}
 MANT = {"bf16": 7, "fp16": 10}
+OBSERVED = {}
 
 
-def assert_close(got, ref, kv, act, valid=None, vmax=1.0):
-    """`vmax`: largest |V| the cache holds.  The stated tolerances are for unit-variance data (|V| <~ 6); attention is
-    a convex combination of V rows, so for the heavy-tailed stress case the tolerance scales with max(1, vmax / 6)."""
+def _dump_observed():
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if OBSERVED and os.path.isdir(d):
+        with open(os.path.join(d, "parity_max_abs.json"), "w") as f:
+            json.dump(OBSERVED, f, indent=1, sort_keys=True)
+
+
+atexit.register(_dump_observed)
+
+
+def assert_close(got, ref, kv, act, valid=None, vmax=None, exact=False, tag=None):
+    """`exact`: ref is the unrounded fp64 definition (half-ulp allowance) rather than a reference rounded to the output dtype
+    (one ulp).  `vmax`: pass the largest |V| of the cache ONLY for heavy-tailed data; it scales TOL by max(1, vmax / 6)."""
     if valid is not None:
         got, ref = got[valid], ref[valid]
     assert not np.isnan(got).any(), "NaN in CUDA output"
     ulp = np.maximum(np.abs(ref), 2.0 ** -14) * 2.0 ** -MANT[act]
     err = np.abs(got - ref)
-    tol = TOL[kv] * max(1.0, vmax / 6.0)
-    bad = err > tol + ulp
-    assert not bad.any(), f"max err {err.max():.3e} (tol {tol} + 1 ulp), {int(bad.sum())} elements out"
+    tol = TOL[kv] * (max(1.0, vmax / 6.0) if vmax is not None else 1.0)
+    small = np.abs(ref) < 0.25
+    allow = np.where(small, tol, tol + (0.5 if exact else 1.0) * ulp)
+    name = tag or os.environ.get("PYTEST_CURRENT_TEST", "?").split("::")[-1].split(" ")[0]
+    rec = OBSERVED.setdefault(name, {})
+    key = "vs_fp64_exact" if exact else "vs_rounded_reference"
+    rec[key] = max(rec.get(key, 0.0), float(err.max()) if err.size else 0.0)
+    rec["max_abs_where_ref_below_0.25"] = max(rec.get("max_abs_where_ref_below_0.25", 0.0), float(err[small].max()) if small.any() else 0.0)
+    rec["tol"] = tol
+    print(f"[parity] {name}: max|err| {err.max() if err.size else 0:.3e} ({key}), where |ref|<0.25: "
+          f"{(err[small].max() if small.any() else 0):.3e}, tol {tol:g}")
+    bad = err > allow
+    assert not bad.any(), f"max err {err.max():.3e} (tol {tol}), {int(bad.sum())} elements out"
 
 
 @pytest.fixture(scope="module")
@@ -56,9 +86,11 @@ def run_case(ops, c, ctas=None, check_write=True, lse=False, fused_merge=True):
     valid = c.lens > 0
     from oracle import oracle as O
 
-    vmax = float(np.nanmax(np.abs(O.e4m3_decode(vc_o))) * float(c.v_scale.max())) if c.fp8 else float(np.abs(vc_o).max())
+    vmax = None
+    if getattr(c, "dist", "normal") == "heavy":   # Student-t(3) stress data only: |V| reaches 30+, the stated tolerances are for unit variance
+        vmax = float(np.nanmax(np.abs(O.e4m3_decode(vc_o))) * float(c.v_scale.max())) if c.fp8 else float(np.abs(vc_o).max())
     assert_close(got, c.oracle_decode(kc_o, vc_o), c.kv, c.act, valid, vmax)           # reference-style rounding points
-    assert_close(got, c.oracle_decode(kc_o, vc_o, "exact"), c.kv, c.act, valid, vmax)  # the mathematical definition (fp64)
+    assert_close(got, c.oracle_decode(kc_o, vc_o, "exact"), c.kv, c.act, valid, vmax, exact=True)  # the mathematical definition (fp64)
     return got, (d_lse.cpu().numpy() if lse else None), (kc_o, vc_o)
 
 
