@@ -40,6 +40,9 @@ PROTOTYPES = {
                                     _i32, _i32, _p, _p, _i32, _p]),
     "b200attn_rope_kv_write": (C.c_int, [_p, _i64, _i64, _i32, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _i32, _i32, _p, _p,
                                          _i64, _i64, _i64, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _i32, _p]),
+    "b200attn_norm_rope_kv_write": (C.c_int, [_p, _i64, _i64, _i32, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _i32, _i32, _i32, _p,
+                                              _i32, _i32, _p, _p, _f32, _p, _p, _i64, _i64, _i64, _p, _i32, _i32, _i32, _i32, _i32,
+                                              _i32, _p, _p, _i32, _p]),
     "b200attn_kv_gather": (C.c_int, [_p, _p, _i32, _i64, _i64, _i64, _i64, _p, _i32, _i32, _i32, _i32, _p, _p]),
     "b200attn_plan_bytes": (_sz, [_i32]),
     "b200attn_default_ctas": (C.c_int, [_i32]),

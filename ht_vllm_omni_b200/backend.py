@@ -373,6 +373,33 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
                                          positions[:n].contiguous(), cos_sin_cache, bool(is_neox), k_cache, v_cache,
                                          layer_slot_mapping[:n], k_scale, v_scale)
 
+    def do_norm_rope_and_kv_cache_update(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                         positions: torch.Tensor, rotary_emb, q_norm, k_norm, kv_cache: torch.Tensor,
+                                         layer_slot_mapping: torch.Tensor) -> None:
+        """The Qwen3 attention prologue in one launch: q_norm / k_norm (per-head RMSNorm), the rotary embedding -- plain, or
+        M-RoPE when `positions` is [3, T] (the Qwen3-Omni thinker, qwen3_omni_moe_thinker.py:1633-1728) -- and the KV write
+        ($VLLM/model_executor/models/qwen3.py:153-160 followed by unified_kv_cache_update).  `rotary_emb` is the layer's
+        RotaryEmbedding / MRotaryEmbedding module (cos_sin_cache, is_neox_style, mrope_section, mrope_interleaved are read
+        from it), `q_norm` / `k_norm` its RMSNorm modules or None.  query / key are updated in place."""
+        k_cache, v_cache = self._planes(kv_cache)
+        k_scale, v_scale = self._scales(layer, key.device)
+        n = min(layer_slot_mapping.shape[0], key.shape[0])
+        cache = rotary_emb.cos_sin_cache
+        if cache.dtype != query.dtype or cache.device != query.device:
+            cache = cache.to(device=query.device, dtype=query.dtype)
+        empty = query.new_empty(0)
+        qw = q_norm.weight.data.to(query.dtype) if q_norm is not None else empty
+        kw = k_norm.weight.data.to(query.dtype) if k_norm is not None else empty
+        eps = float(getattr(q_norm if q_norm is not None else k_norm, "variance_epsilon", 0.0)) if (q_norm is not None or k_norm is not None) else 0.0
+        pos = positions[..., :n].contiguous()
+        section = list(getattr(rotary_emb, "mrope_section", None) or [0, 0, 0])
+        torch.ops.b200attn.norm_rope_kv_write(query[:n].view(n, self.num_heads, self.head_size),
+                                              key[:n].view(n, self.num_kv_heads, self.head_size),
+                                              value[:n].view(n, self.num_kv_heads, self.head_size), pos, cache,
+                                              bool(rotary_emb.is_neox_style), qw, kw, eps, section,
+                                              bool(getattr(rotary_emb, "mrope_interleaved", False)), k_cache, v_cache,
+                                              layer_slot_mapping[:n], k_scale, v_scale)
+
     def forward(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
                 kv_cache: torch.Tensor, attn_metadata: B200PagedAttentionMetadata, output: torch.Tensor,
                 output_scale: torch.Tensor | None = None, output_block_scale: torch.Tensor | None = None) -> torch.Tensor:

@@ -27,7 +27,11 @@ struct RopeKvParams {
   const void* value;
   int64_t q_stride_t, q_stride_h, key_stride_t, key_stride_h, value_stride_t, value_stride_h;
   const int64_t* positions;
+  int64_t pos_axis_stride;   // 0: positions [T]; else positions [3][T] (M-RoPE: temporal / height / width), this many elements apart
   const void* cos_sin;   // [max_pos][rot]: cos (rot/2) then sin (rot/2), activation dtype
+  const void* q_norm_w;  // nullable: RMSNorm weight [D] applied to every q head before the rotation (Qwen3 q_norm)
+  const void* k_norm_w;  // nullable: likewise for k (k_norm)
+  float rms_eps;
   void* k_cache;
   void* v_cache;
   int64_t stride_block, stride_slot, stride_head;
@@ -36,6 +40,7 @@ struct RopeKvParams {
   const float* v_scale;
   int scale_stride;
   int T, Hq, Hkv, D, rot, block_size, is_neox, each_op;
+  int sec_t, sec_h, sec_w, interleaved;   // M-RoPE sections (frequency counts per axis, sum = rot / 2); all 0 = plain RoPE
 };
 
 template <int DT>
@@ -88,6 +93,20 @@ __device__ __forceinline__ uint2 quant8(const float (&f)[8], float scale) {
   return make_uint2(w[0], w[1]);
 }
 
+// M-RoPE: which position axis (0 temporal, 1 height, 2 width) drives rotary frequency `f`
+// ($VLLM/model_executor/layers/rotary_embedding/mrope.py: forward_native :286-298 chunked [TTT..HHH..WWW],
+// apply_interleaved_rope :190-198 [THWTHW...TT])
+__device__ __forceinline__ int mrope_axis(const RopeKvParams& p, int f) {
+  if (p.sec_t + p.sec_h + p.sec_w == 0) return 0;
+  if (p.interleaved) {
+    const int m = f % 3;
+    if (m == 1 && f < 3 * p.sec_h) return 1;
+    if (m == 2 && f < 3 * p.sec_w) return 2;
+    return 0;
+  }
+  return f < p.sec_t ? 0 : (f < p.sec_t + p.sec_h ? 1 : 2);
+}
+
 template <int DT, bool FP8>
 __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p) {
   using E = Elem<DT>;
@@ -99,9 +118,13 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
   const int j = (int)(gid - row * lanes);
   pdl_launch_dependents();
   pdl_wait();
-  if (row >= (uint32_t)p.T * units) return;
-  const int t = (int)(row / units);
-  const int u = (int)(row - (uint32_t)t * units);
+  // With a fused RMSNorm the D/16 threads of a row reduce its sum of squares by warp shuffles (D/16 divides 32 and rows are
+  // aligned to it), so no thread may leave before that point; without it the early exits below are taken as before.
+  const bool any_norm = p.q_norm_w != nullptr || p.k_norm_w != nullptr;
+  bool live = row < (uint32_t)p.T * units;
+  if (!any_norm && !live) return;
+  const int t = live ? (int)(row / units) : 0;
+  const int u = live ? (int)(row - (uint32_t)t * units) : 0;
   const int kind = u < p.Hq ? 0 : (u < p.Hq + p.Hkv ? 1 : 2);   // q, k, v
   const int h = kind == 0 ? u : (kind == 1 ? u - p.Hq : u - p.Hq - p.Hkv);
   // slot, position and the data vectors are independent loads, issued together (see kv_write.cu)
@@ -110,25 +133,77 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
 
   const int half = p.rot >> 1;
   const bool rotary = kind != 2 && j < (p.rot >> 4);
+  const void* norm_w = kind == 0 ? p.q_norm_w : (kind == 1 ? p.k_norm_w : nullptr);
   int a0, a1;
   if (rotary && p.is_neox) { a0 = 8 * j; a1 = half + 8 * j; }
   else if (rotary) { a0 = 16 * j; a1 = a0 + 8; }
   else { a0 = (kind == 2 ? 0 : p.rot) + 16 * (j - (kind == 2 ? 0 : (p.rot >> 4))); a1 = a0 + 8; }
-  if (kind == 0 && !rotary) return;   // q elements beyond the rotary span stay as they are
+  if (kind == 0 && !rotary && norm_w == nullptr) live = false;   // q elements beyond the rotary span stay as they are
+  if (!any_norm && !live) return;
 
   void* base = kind == 0 ? p.query : (kind == 1 ? p.key : const_cast<void*>(p.value));
   const int64_t roff = kind == 0 ? (int64_t)t * p.q_stride_t + (int64_t)h * p.q_stride_h
                      : kind == 1 ? (int64_t)t * p.key_stride_t + (int64_t)h * p.key_stride_h
                                  : (int64_t)t * p.value_stride_t + (int64_t)h * p.value_stride_h;
   float c0[8], c1[8];
-  load8<DT>(base, roff + a0, c0);
-  load8<DT>(base, roff + a1, c1);
-  if (kind == 2 && slot < 0) return;   // padding token: nothing to write
+  if (live) {
+    load8<DT>(base, roff + a0, c0);
+    load8<DT>(base, roff + a1, c1);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c0[i] = c1[i] = 0.f;
+  }
+  if (kind == 2 && slot < 0) live = false;   // padding token: nothing to write
+  if (!any_norm && !live) return;
+
+  if (any_norm) {
+    // ---- RMSNorm over the head ($VLLM/model_executor/layers/layernorm.py forward_native / csrc/layernorm_kernels.cu):
+    //   y = rnd(rnd(x * rsqrt(mean(x^2) + eps)) * w)   -- fp32 statistics, the normalised value rounded to the activation
+    // dtype BEFORE the multiplication by the weight, which is itself a 16-bit multiply (one more rounding)
+    float ss = 0.f;
+    if (live && norm_w != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ss += c0[i] * c0[i] + c1[i] * c1[i];
+    }
+    for (uint32_t off = 1; off < lanes; off <<= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+    if (!live) return;
+    if (norm_w != nullptr) {
+      const float inv = rsqrtf(ss / (float)p.D + p.rms_eps);
+      float w0[8], w1[8];
+      load8<DT>(norm_w, a0, w0);
+      load8<DT>(norm_w, a1, w1);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        c0[i] = rnd<DT>(rnd<DT>(c0[i] * inv) * w0[i]);
+        c1[i] = rnd<DT>(rnd<DT>(c1[i] * inv) * w1[i]);
+      }
+    }
+  }
 
   if (rotary) {
     float cs[8], sn[8];
-    load8<DT>(p.cos_sin, pos * p.rot + 8 * j, cs);
-    load8<DT>(p.cos_sin, pos * p.rot + half + 8 * j, sn);
+    if (p.pos_axis_stride == 0) {
+      load8<DT>(p.cos_sin, pos * p.rot + 8 * j, cs);
+      load8<DT>(p.cos_sin, pos * p.rot + half + 8 * j, sn);
+    } else {
+      // M-RoPE: frequency f takes cos / sin from the cache row of ITS axis' position; a chunk of 8 frequencies can touch all
+      // three rows (interleaved layout), each fetched only when one of its frequencies needs it
+      int ax[8];
+      int need = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { ax[i] = mrope_axis(p, 8 * j + i); need |= 1 << ax[i]; }
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        if (!(need & (1 << a))) continue;
+        const int64_t pa = a == 0 ? pos : __ldg(p.positions + (int64_t)a * p.pos_axis_stride + t);
+        float ca[8], sa[8];
+        load8<DT>(p.cos_sin, pa * p.rot + 8 * j, ca);
+        load8<DT>(p.cos_sin, pa * p.rot + half + 8 * j, sa);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (ax[i] == a) { cs[i] = ca[i]; sn[i] = sa[i]; }
+      }
+    }
     if (p.is_neox) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -149,7 +224,9 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
 #pragma unroll
       for (int i = 0; i < 8; ++i) { c0[i] = e[i]; c1[i] = e[8 + i]; }
     }
-    // rotated q / k go back in place, like torch.ops._C.rotary_embedding
+  }
+  if (rotary || (kind != 2 && norm_w != nullptr)) {
+    // rotated (and normalised) q / k go back in place, like torch.ops._C.rotary_embedding / fused_qk_norm_rope
     typename E::type* dst = reinterpret_cast<typename E::type*>(base) + roff;
     *reinterpret_cast<uint4*>(dst + a0) = pack8<DT>(c0);
     *reinterpret_cast<uint4*>(dst + a1) = pack8<DT>(c1);
@@ -177,15 +254,34 @@ int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaSt
 
 using namespace b200attn;
 
-extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads, void* key,
-                                      const void* value, int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t,
-                                      int64_t value_stride_h, const int64_t* positions, const void* cos_sin_cache,
-                                      int32_t rotary_dim, int32_t rope_flags, void* k_cache, void* v_cache, int64_t stride_block,
-                                      int64_t stride_slot, int64_t stride_head, const int64_t* slot_mapping,
-                                      int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
-                                      int32_t in_dtype, int32_t kv_dtype, const float* k_scale, const float* v_scale,
-                                      int32_t scale_stride, void* stream) {
+static int rope_impl(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads, void* key,
+                     const void* value, int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t,
+                     int64_t value_stride_h, const int64_t* positions, int64_t positions_axis_stride, int32_t sec_t, int32_t sec_h,
+                     int32_t sec_w, const void* cos_sin_cache,
+                     int32_t rotary_dim, int32_t rope_flags, const void* q_norm_weight, const void* k_norm_weight, float rms_eps,
+                     void* k_cache, void* v_cache, int64_t stride_block,
+                     int64_t stride_slot, int64_t stride_head, const int64_t* slot_mapping,
+                     int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                     int32_t in_dtype, int32_t kv_dtype, const float* k_scale, const float* v_scale,
+                     int32_t scale_stride, void* stream) {
   if (num_tokens == 0) return B200ATTN_OK;
+  if (positions_axis_stride != 0) {
+    if (sec_t < 0 || sec_h < 0 || sec_w < 0 || sec_t + sec_h + sec_w != rotary_dim / 2) {
+      set_error("rope_kv_write: mrope_section (%d, %d, %d) must be non-negative and sum to rotary_dim / 2 = %d", sec_t, sec_h, sec_w,
+                rotary_dim / 2);
+      return B200ATTN_EINVAL;
+    }
+  } else {
+    sec_t = sec_h = sec_w = 0;
+  }
+  if ((q_norm_weight || k_norm_weight) && (head_dim > 512 || (head_dim & (head_dim - 1)) != 0)) {
+    set_error("rope_kv_write: the fused RMSNorm needs a power-of-two head_dim <= 512 (got %d)", head_dim);
+    return B200ATTN_EINVAL;
+  }
+  if ((q_norm_weight && (reinterpret_cast<uintptr_t>(q_norm_weight) % 16)) || (k_norm_weight && (reinterpret_cast<uintptr_t>(k_norm_weight) % 16))) {
+    set_error("rope_kv_write: norm weights must be 16-byte aligned");
+    return B200ATTN_EINVAL;
+  }
   if (!query || !key || !value || !positions || !cos_sin_cache || !k_cache || !v_cache || !slot_mapping) {
     set_error("rope_kv_write: null pointer argument");
     return B200ATTN_EINVAL;
@@ -227,6 +323,10 @@ extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q
   p.key_stride_t = key_stride_t; p.key_stride_h = key_stride_h;
   p.value_stride_t = value_stride_t; p.value_stride_h = value_stride_h;
   p.positions = positions; p.cos_sin = cos_sin_cache;
+  p.pos_axis_stride = positions_axis_stride;
+  p.sec_t = sec_t; p.sec_h = sec_h; p.sec_w = sec_w;
+  p.interleaved = (rope_flags & B200ATTN_ROPE_MROPE_INTERLEAVED) ? 1 : 0;
+  p.q_norm_w = q_norm_weight; p.k_norm_w = k_norm_weight; p.rms_eps = rms_eps;
   p.k_cache = k_cache; p.v_cache = v_cache;
   p.stride_block = stride_block; p.stride_slot = stride_slot; p.stride_head = stride_head;
   p.slot_mapping = slot_mapping; p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;
@@ -249,4 +349,34 @@ extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q
     fn = in_dtype == B200ATTN_BF16 ? (const void*)rope_kv_write_kernel<B200ATTN_BF16, false> : (const void*)rope_kv_write_kernel<B200ATTN_FP16, false>;
   void* args[] = {&p};
   return launch_with_pdl(fn, dim3((unsigned)grid), dim3(block), 0, static_cast<cudaStream_t>(stream), args);
+}
+
+extern "C" int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads, void* key,
+                                      const void* value, int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t,
+                                      int64_t value_stride_h, const int64_t* positions, const void* cos_sin_cache,
+                                      int32_t rotary_dim, int32_t rope_flags, void* k_cache, void* v_cache, int64_t stride_block,
+                                      int64_t stride_slot, int64_t stride_head, const int64_t* slot_mapping,
+                                      int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                                      int32_t in_dtype, int32_t kv_dtype, const float* k_scale, const float* v_scale,
+                                      int32_t scale_stride, void* stream) {
+  return rope_impl(query, q_stride_t, q_stride_h, num_q_heads, key, value, key_stride_t, key_stride_h, value_stride_t, value_stride_h,
+                   positions, 0, 0, 0, 0, cos_sin_cache, rotary_dim, rope_flags, nullptr, nullptr, 0.f, k_cache, v_cache, stride_block,
+                   stride_slot, stride_head, slot_mapping, num_tokens, num_kv_heads, head_dim, block_size, in_dtype, kv_dtype, k_scale,
+                   v_scale, scale_stride, stream);
+}
+
+extern "C" int b200attn_norm_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads, void* key,
+                                           const void* value, int64_t key_stride_t, int64_t key_stride_h, int64_t value_stride_t,
+                                           int64_t value_stride_h, const int64_t* positions, int64_t positions_axis_stride,
+                                           int32_t mrope_t, int32_t mrope_h, int32_t mrope_w, const void* cos_sin_cache,
+                                           int32_t rotary_dim, int32_t rope_flags, const void* q_norm_weight,
+                                           const void* k_norm_weight, float rms_eps, void* k_cache, void* v_cache,
+                                           int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                                           const int64_t* slot_mapping, int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim,
+                                           int32_t block_size, int32_t in_dtype, int32_t kv_dtype, const float* k_scale,
+                                           const float* v_scale, int32_t scale_stride, void* stream) {
+  return rope_impl(query, q_stride_t, q_stride_h, num_q_heads, key, value, key_stride_t, key_stride_h, value_stride_t, value_stride_h,
+                   positions, positions_axis_stride, mrope_t, mrope_h, mrope_w, cos_sin_cache, rotary_dim, rope_flags, q_norm_weight,
+                   k_norm_weight, rms_eps, k_cache, v_cache, stride_block, stride_slot, stride_head, slot_mapping, num_tokens,
+                   num_kv_heads, head_dim, block_size, in_dtype, kv_dtype, k_scale, v_scale, scale_stride, stream);
 }

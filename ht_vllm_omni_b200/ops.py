@@ -149,6 +149,59 @@ def _(query, key, value, positions, cos_sin_cache, is_neox, k_cache, v_cache, sl
     return None
 
 
+@torch.library.custom_op("b200attn::norm_rope_kv_write", mutates_args=("query", "key", "k_cache", "v_cache"), device_types="cuda")
+def norm_rope_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, positions: torch.Tensor,
+                       cos_sin_cache: torch.Tensor, is_neox: bool, q_norm_weight: torch.Tensor, k_norm_weight: torch.Tensor,
+                       rms_eps: float, mrope_section: list[int], mrope_interleaved: bool, k_cache: torch.Tensor,
+                       v_cache: torch.Tensor, slot_mapping: torch.Tensor, k_scale: torch.Tensor, v_scale: torch.Tensor,
+                       round_each_op: bool = False) -> None:
+    """q/k RMSNorm + rotary embedding (plain or M-RoPE) + KV write in one launch (b200attn_norm_rope_kv_write).
+    positions: int64 [T] or [3, T] (then `mrope_section` = [t, h, w] frequency counts, sum = rotary_dim / 2);
+    q_norm_weight / k_norm_weight: [D] in the activation dtype, or EMPTY tensors for no normalisation.  Rest as rope_kv_write."""
+    _require_cuda(query, key, value, positions, cos_sin_cache, k_cache, v_cache, slot_mapping)
+    lib = load_library()
+    T = slot_mapping.shape[0]
+    if T == 0:
+        return
+    if query.dim() != 3 or key.dim() != 3 or value.shape != key.shape or query.stride(2) != 1 or key.stride(2) != 1 or value.stride(2) != 1:
+        raise B200AttnError("query/key/value must be [T, H, D] with contiguous head_dim")
+    if positions.dtype != torch.int64 or positions.dim() not in (1, 2) or positions.stride(-1) != 1 or positions.shape[-1] < T:
+        raise B200AttnError("positions must be int64 [T] or [3, T] with contiguous rows")
+    if positions.dim() == 2 and (positions.shape[0] != 3 or len(mrope_section) != 3):
+        raise B200AttnError("2-D positions must be [3, T] and come with mrope_section = [t, h, w]")
+    if query.shape[0] < T or key.shape[0] < T:
+        raise B200AttnError("query/key/value must cover every slot_mapping entry")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous():
+        raise B200AttnError("slot_mapping must be contiguous int64")
+    if cos_sin_cache.dtype != query.dtype or key.dtype != query.dtype or value.dtype != query.dtype or not cos_sin_cache.is_contiguous():
+        raise B200AttnError("cos_sin_cache, key and value must have the query dtype (cos_sin_cache contiguous)")
+    Hq, Hkv, D = query.shape[1], key.shape[1], key.shape[2]
+    qw = q_norm_weight if q_norm_weight.numel() > 0 else None
+    kw = k_norm_weight if k_norm_weight.numel() > 0 else None
+    for w in (qw, kw):
+        if w is not None and (w.dtype != query.dtype or w.numel() != D or not w.is_contiguous() or not w.is_cuda):
+            raise B200AttnError("norm weights must be contiguous CUDA tensors of [head_dim] in the query dtype")
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    kvdt = _dt(k_cache)
+    sstride = _scale_stride(k_scale, Hkv, v_scale) if kvdt == DT_FP8_E4M3 else 0
+    mrope = positions.dim() == 2
+    sec = [int(x) for x in mrope_section] if mrope else [0, 0, 0]
+    flags = (1 if is_neox else 0) | (2 if round_each_op else 0) | (4 if (mrope and mrope_interleaved) else 0)
+    check(lib.b200attn_norm_rope_kv_write(
+        query.data_ptr(), query.stride(0), query.stride(1), Hq, key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1),
+        value.stride(0), value.stride(1), positions.data_ptr(), positions.stride(0) if mrope else 0, sec[0], sec[1], sec[2],
+        cos_sin_cache.data_ptr(), cos_sin_cache.shape[1], flags, qw.data_ptr() if qw is not None else None,
+        kw.data_ptr() if kw is not None else None, float(rms_eps), k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh,
+        slot_mapping.data_ptr(), T, Hkv, D, k_cache.shape[1], _dt(query), kvdt, k_scale.data_ptr(), v_scale.data_ptr(), sstride,
+        _stream(query)), "b200attn_norm_rope_kv_write")
+
+
+@norm_rope_kv_write.register_fake
+def _(query, key, value, positions, cos_sin_cache, is_neox, q_norm_weight, k_norm_weight, rms_eps, mrope_section, mrope_interleaved,
+      k_cache, v_cache, slot_mapping, k_scale, v_scale, round_each_op=False) -> None:
+    return None
+
+
 # ------------------------------------------------------------------------------------------------
 # decode_plan (once per step) and paged_decode (= split-KV decode kernel + merge kernel)
 # ------------------------------------------------------------------------------------------------

@@ -51,6 +51,7 @@ extern "C" {
 /* b200attn_rope_kv_write flags */
 #define B200ATTN_ROPE_NEOX 1           /* partners are the halves of the rotary span (else even / odd elements) */
 #define B200ATTN_ROPE_ROUND_EACH_OP 2  /* torch-native rounding of every elementary op (default: fp32, one rounding) */
+#define B200ATTN_ROPE_MROPE_INTERLEAVED 4 /* M-RoPE sections interleaved [THWTHW...TT] instead of chunked [T..H..W..] */
 
 #define B200ATTN_DECODE_FUSED_MERGE 1 /* merge split-KV partials inside the decode kernel (no b200attn_merge call) */
 
@@ -109,6 +110,41 @@ B200ATTN_API int b200attn_rope_kv_write(void* query, int64_t q_stride_t, int64_t
                            int64_t key_stride_t, int64_t key_stride_h,
                            int64_t value_stride_t, int64_t value_stride_h,
                            const int64_t* positions, const void* cos_sin_cache, int32_t rotary_dim, int32_t rope_flags,
+                           void* k_cache, void* v_cache,
+                           int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                           const int64_t* slot_mapping, int32_t num_tokens,
+                           int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                           int32_t in_dtype, int32_t kv_dtype,
+                           const float* k_scale, const float* v_scale, int32_t scale_stride,
+                           void* stream);
+
+/*
+ * Kernel 1c -- q/k RMSNorm + (multimodal) rotary embedding + KV write, one launch: b200attn_rope_kv_write with the two steps
+ * the Qwen3 stages put around it.
+ * Replaces: q_norm / k_norm ($VLLM/model_executor/models/qwen3.py:153-158; RMSNorm.forward,
+ *   $VLLM/model_executor/layers/layernorm.py, csrc/layernorm_kernels.cu), the rotary embedding -- RotaryEmbedding.forward or,
+ *   for the Qwen3-Omni thinker's 3-axis positions (vllm_omni/model_executor/models/qwen3_omni/qwen3_omni_moe_thinker.py:
+ *   1633-1728), MRotaryEmbedding.forward ($VLLM/model_executor/layers/rotary_embedding/mrope.py:263-360) -- and
+ *   reshape_and_cache_flash; the sequence vLLM itself fuses as fused_qk_norm_rope + unified_kv_cache_update.
+ *
+ *   q_norm_weight / k_norm_weight  nullable, [head_dim] in the activation dtype: every q (k) head becomes
+ *                          rnd(rnd(x * rsqrt(mean(x^2) + rms_eps)) * w) before the rotation (fp32 statistics, the two roundings
+ *                          of the reference's kernel); elements beyond rotary_dim are normalised too.  In place.
+ *   positions_axis_stride  0: positions is int64 [T] (plain RoPE, mrope_* ignored);
+ *                          else positions is int64 [3][T] (temporal, height, width), axes this many elements apart, and rotary
+ *                          frequency f reads cos / sin from the cache row of the position of ITS axis: chunked sections
+ *                          [0, t) -> T, [t, t + h) -> H, rest -> W, or interleaved (B200ATTN_ROPE_MROPE_INTERLEAVED): f % 3 == 1
+ *                          and f < 3 h -> H, f % 3 == 2 and f < 3 w -> W, else T.  mrope_t + mrope_h + mrope_w = rotary_dim / 2.
+ * Everything else as b200attn_rope_kv_write.
+ */
+B200ATTN_API int b200attn_norm_rope_kv_write(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_t num_q_heads,
+                           void* key, const void* value,
+                           int64_t key_stride_t, int64_t key_stride_h,
+                           int64_t value_stride_t, int64_t value_stride_h,
+                           const int64_t* positions, int64_t positions_axis_stride,
+                           int32_t mrope_t, int32_t mrope_h, int32_t mrope_w,
+                           const void* cos_sin_cache, int32_t rotary_dim, int32_t rope_flags,
+                           const void* q_norm_weight, const void* k_norm_weight, float rms_eps,
                            void* k_cache, void* v_cache,
                            int64_t stride_block, int64_t stride_slot, int64_t stride_head,
                            const int64_t* slot_mapping, int32_t num_tokens,

@@ -171,6 +171,55 @@ def rope_ref(x, positions, cos_sin_cache, rotary_dim: int, is_neox: bool, act: s
     return out
 
 
+def mrope_axes(rotary_dim: int, mrope_section, interleaved: bool) -> np.ndarray:
+    """Position axis (0 temporal, 1 height, 2 width) of every rotary frequency 0 .. rotary_dim/2 - 1
+    ($VLLM/model_executor/layers/rotary_embedding/mrope.py: chunked split of forward_native :291-298; interleaved layout
+    of apply_interleaved_rope :190-198: x_t[1 : 3h : 3] <- H, x_t[2 : 3w : 3] <- W)."""
+    half = rotary_dim // 2
+    t, h, w = (int(x) for x in mrope_section)
+    assert t + h + w == half
+    ax = np.zeros(half, dtype=np.int64)
+    if interleaved:
+        ax[1:3 * h:3] = 1
+        ax[2:3 * w:3] = 2
+    else:
+        ax[t:t + h] = 1
+        ax[t + h:] = 2
+    return ax
+
+
+def mrope_ref(x, positions3, cos_sin_cache, rotary_dim: int, is_neox: bool, act: str, mrope_section, interleaved: bool,
+              each_op: bool = False) -> np.ndarray:
+    """M-RoPE (MRotaryEmbedding.forward_native, mrope.py:263-322): positions3 int64 [3, T]; frequency f of token t takes its
+    cos / sin from cos_sin_cache[positions3[axis(f), t]]; the rotation itself is rope_ref's."""
+    x = np.asarray(x, dtype=np.float32)
+    half = rotary_dim // 2
+    cache = np.asarray(cos_sin_cache, dtype=np.float32)
+    p3 = np.asarray(positions3, dtype=np.int64)
+    ax = mrope_axes(rotary_dim, mrope_section, interleaved)
+    T = p3.shape[1]
+    rows = p3[ax[None, :].repeat(T, 0), np.arange(T)[:, None]]            # [T, half]: cache row per (token, frequency)
+    f = np.arange(half)[None, :]
+    table = np.concatenate([cache[rows, f], cache[rows, half + f]], axis=1)   # per-token [cos | sin] rows
+    out = np.empty_like(x)
+    for t in range(T):   # rope_ref with a one-row "cache" per token
+        out[t:t + 1] = rope_ref(x[t:t + 1], np.zeros(1, np.int64), table[t:t + 1], rotary_dim, is_neox, act, each_op)
+    return out
+
+
+def rms_norm_ref(x, weight, eps: float, act: str) -> np.ndarray:
+    """RMSNorm over the last axis as the reference computes it for 16-bit activations (RMSNorm.forward_native,
+    $VLLM/model_executor/layers/layernorm.py; csrc/layernorm_kernels.cu rms_norm_kernel): statistics in fp32,
+        y = rnd(rnd(x * rsqrt(mean(x^2) + eps)) * w)
+    x float32 [..., D] holding activation-dtype values, weight [D] likewise.  The fp32 sum's association order is the
+    reference's implementation detail (block reduce / pairwise), so comparisons allow one unit in the last place."""
+    x = np.asarray(x, dtype=np.float32)
+    var = np.mean(x.astype(np.float64) ** 2, axis=-1, keepdims=True).astype(np.float32)
+    inv = (1.0 / np.sqrt(var.astype(np.float64) + np.float64(np.float32(eps)))).astype(np.float32)
+    y = act_round((x * inv).astype(np.float32), act)
+    return act_round((y * np.asarray(weight, dtype=np.float32)).astype(np.float32), act)
+
+
 def rope_kv_write_ref(query, key, value, positions, cos_sin_cache, rotary_dim, is_neox, act, k_cache, v_cache, slot_mapping,
                       k_scale=None, v_scale=None, fp8=False, each_op=False):
     """Returns (q', k'); k' and value are written to the cache exactly as kv_write_ref does."""
