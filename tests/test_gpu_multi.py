@@ -33,7 +33,7 @@ def test_sequence_split_exchange_matches_unsharded_on_two_gpus():
     _need(2)
     r = _torchrun(os.path.join("tests", "tools", "dcp_check.py"), 2, 29611)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert "over NCCL: max |sequence-split - unsharded|" in r.stdout and "over NVLink peer memory" in r.stdout, r.stdout[-2000:]
+    assert "over NCCL: max |sequence-split - unsharded|" in r.stdout and "over NVLink peer memory" in r.stdout and "over NVLink pushes" in r.stdout, r.stdout[-2000:]
 
 
 def test_strong_scaled_thinker_block_on_two_gpus():

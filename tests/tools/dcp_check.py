@@ -112,6 +112,47 @@ if rank == 0:
     print(f"dcp{world} over NVLink peer memory: max |sequence-split - unsharded| = {t2.item():.5f}; decode+combine "
           f"{e0.elapsed_time(e1) / 20 * 1e3:.1f} us per layer, of which barrier + peer-load merge {comb:.1f} us", flush=True)
 assert t2.item() <= 1e-2, t2.item()
+# ---- push exchange: query heads pushed to the peers' gather buffers, partial slices pushed to the peers' receive buffers ----
+pp = P.PushExchange(B, Hl, D, torch.bfloat16, dev)
+
+
+def layer_push():
+    qg = pp.gather_q(q_local)
+    o_p, l_p = pp.partial_buffers(B)
+    ws.decode(qg, kc, vc, bt, ln, o_p, ks, vs, D ** -0.5, lse=l_p)
+    return pp.combine(B)
+
+
+got3 = layer_push()
+assert torch.equal(pp.gather[pp.slot, :B].cpu(), q_all), "pushed query heads differ from the all-gathered ones"
+for _ in range(3):
+    got3 = layer_push()
+torch.cuda.synchronize(); dist.barrier()
+# replayed as a CUDA graph too (flags are launch counters: nothing to reset between replays)
+side = torch.cuda.Stream(device=dev); side.wait_stream(torch.cuda.current_stream())
+with torch.cuda.stream(side):
+    layer_push(); layer_push()
+torch.cuda.current_stream().wait_stream(side); torch.cuda.synchronize(); dist.barrier()
+gr = torch.cuda.CUDAGraph()
+with torch.cuda.graph(gr):
+    got3 = layer_push()
+    got3b = layer_push()
+for _ in range(3):
+    gr.replay()
+torch.cuda.synchronize(); dist.barrier()
+e0, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
+e0.record()
+for _ in range(10):
+    gr.replay()
+e1.record(); torch.cuda.synchronize()
+err3 = max((got3.float() - full_out[:, rank * Hl:(rank + 1) * Hl].float()).abs().max().item(),
+           (got3b.float() - full_out[:, rank * Hl:(rank + 1) * Hl].float()).abs().max().item())
+t3 = torch.tensor([err3], device=dev); dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+if rank == 0:
+    print(f"dcp{world} over NVLink pushes (gather_q + decode + combine, graph replay): max |sequence-split - unsharded| = {t3.item():.5f}; "
+          f"{e0.elapsed_time(e1) / 20 * 1e3:.1f} us per layer", flush=True)
+assert t3.item() <= 1e-2, t3.item()
+assert torch.equal(got3, got2), "push combine and pull combine disagree"
 dist.barrier(); torch.cuda.synchronize()
 sys.stdout.flush()
 os._exit(0)

@@ -132,18 +132,13 @@ def run_sharded(dev, rank, world, lib):
         q_local = q_group[:, rr * hq_local:(rr + 1) * hq_local].contiguous()
         ws = ops.DecodeWorkspace(dev, B, torch.uint8, head_dim=D, group_size=hq_per_kv)
         ws.make_plan(lens_l, hg, 1, bt_l, BS)
-        px = PAR.PeerExchange(B, hg, D, torch.bfloat16, dev, group=grp)
+        px = PAR.PushExchange(B, hq_local, D, torch.bfloat16, dev, group=grp)
         outs = [None] * LAYERS
-        qg_buf = torch.empty(replicas * B, hq_local, D, dtype=torch.bfloat16, device=dev)
-
-        def gather_q():
-            dist.all_gather_into_tensor(qg_buf, q_local, group=grp)
-            return qg_buf.view(replicas, B, hq_local, D).permute(1, 0, 2, 3).reshape(B, hg, D)
 
         def layers(exchange=True):
             for l in range(LAYERS):
-                qg = gather_q() if exchange else q_group
-                o_buf, lse_buf = px.buffers()
+                qg = px.gather_q(q_local) if exchange else q_group
+                o_buf, lse_buf = px.partial_buffers(B)
                 ws.decode(qg, planes[l][0], planes[l][1], bt_l, lens_l, o_buf, ks_l, vs_l, D ** -0.5, lse=lse_buf)
                 if exchange:
                     outs[l] = px.combine(B)
@@ -155,9 +150,28 @@ def run_sharded(dev, rank, world, lib):
         got = torch.stack(outs)
         h0 = hq0 + rr * hq_local
         err = float((got.float() - ref[:, :, h0:h0 + hq_local].float()).abs().max())
+        # the same layers with the round-1 exchange for comparison: NCCL all-gather of the query heads + symmetric-memory
+        # barrier + peer-LOAD merge (parallel.PeerExchange)
+        pl = PAR.PeerExchange(B, hg, D, torch.bfloat16, dev, group=grp)
+        qg_buf = torch.empty(replicas * B, hq_local, D, dtype=torch.bfloat16, device=dev)
+
+        def layers_pull():
+            for l in range(LAYERS):
+                dist.all_gather_into_tensor(qg_buf, q_local, group=grp)
+                qg = qg_buf.view(replicas, B, hq_local, D).permute(1, 0, 2, 3).reshape(B, hg, D)
+                o_buf, lse_buf = pl.buffers()
+                ws.decode(qg, planes[l][0], planes[l][1], bt_l, lens_l, o_buf, ks_l, vs_l, D ** -0.5, lse=lse_buf)
+                pl.combine(B)
+
+        try:
+            t_pull, _ = _time(layers_pull, dev)
+        except Exception:  # noqa: BLE001
+            t_pull = None
         res.update({"layout": f"tp{world}: KV head x {replicas}-way sequence split (16-token interleave); per rank {hq_local} query heads, "
-                              f"half the context of one KV head; query all-gather (NCCL) + (o, lse) combine over NVLink peer memory",
-                    "t_us_per_layer": tn, "decode_only_us_per_layer": td, "exchange_us_per_layer": tn - td})
+                              f"half the context of one KV head; query heads and (o, lse) partial slices PUSHED over NVLink peer memory "
+                              f"(two flag-synchronised launches per layer, no collective)",
+                    "t_us_per_layer": tn, "decode_only_us_per_layer": td, "exchange_us_per_layer": tn - td,
+                    "nccl_allgather_plus_peer_load_merge_us_per_layer": t_pull})
     e = torch.tensor([err], device=dev, dtype=torch.float64)
     dist.all_reduce(e, op=dist.ReduceOp.MAX)
     res.update({"efficiency": t1 / (world * tn), "speedup": t1 / tn, "gbs_aggregate": dec_bytes_full / tn / 1e3,
