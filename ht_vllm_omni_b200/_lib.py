@@ -39,6 +39,8 @@ PROTOTYPES = {
     "b200attn_sm_count": (C.c_int, []),
     "b200attn_kv_write": (C.c_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _i64, _i64, _i64, _p, _i32, _i32, _i32, _i32,
                                     _i32, _i32, _p, _p, _i32, _p]),
+    "b200attn_kv_write_per_token_head": (C.c_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _i64, _i64, _i64, _p, _p, _i64, _i64, _i64,
+                                                   _p, _i32, _i32, _i32, _i32, _i32, _i32, _p]),
     "b200attn_rope_kv_write": (C.c_int, [_p, _i64, _i64, _i32, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _i32, _i32, _p, _p,
                                          _i64, _i64, _i64, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _i32, _p]),
     "b200attn_norm_rope_kv_write": (C.c_int, [_p, _i64, _i64, _i32, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _i32, _i32, _i32, _p,
@@ -54,6 +56,9 @@ PROTOTYPES = {
     "b200attn_decode_kv_write": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _i64, _i64, _i64,
                                            _i64, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32,
                                            _p, _sz, _p, _p, _i32, _i32, _p]),
+    "b200attn_decode_per_token_head": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _i64, _i64, _i64,
+                                                 _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32, _p, _sz, _p, _p,
+                                                 _i32, _i32, _p]),
     "b200attn_merge": (C.c_int, [_p, _i32, _p, _p, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p]),
     "b200attn_merge_lse": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
     "b200attn_merge_lse_peers": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),

@@ -52,6 +52,7 @@ from ._lib import B200AttnError
 
 BACKEND_PATH = "ht_vllm_omni_b200.backend.B200PagedAttentionBackend"
 _FP8_NAMES = ("fp8", "fp8_e4m3")
+PER_TOKEN_HEAD = "fp8_per_token_head"   # dynamic per-(token, head) scales in float32 side caches (vLLM >= 0.20, KVQuantMode.FP8_PER_TOKEN_HEAD)
 
 
 def is_fp8_kv(kv_cache_dtype: str) -> bool:
@@ -83,7 +84,7 @@ class B200PagedAttentionBackend(AttentionBackend):
 
     accept_output_buffer: bool = True
     supported_dtypes: ClassVar[list[torch.dtype]] = [torch.float16, torch.bfloat16]
-    supported_kv_cache_dtypes: ClassVar[list[str]] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3"]
+    supported_kv_cache_dtypes: ClassVar[list[str]] = ["auto", "float16", "bfloat16", "fp8", "fp8_e4m3", PER_TOKEN_HEAD]
     # forward() writes the step's new tokens itself: on a pure-decode step the store happens INSIDE the decode kernel
     # (b200attn_decode_kv_write: one launch per layer, no kernel boundary between the write and the read); the reference's
     # runner then hands forward() the unpadded slot_mapping (vllm_omni/worker/gpu_ar_model_runner.py:231-244, the same switch
@@ -120,6 +121,10 @@ class B200PagedAttentionBackend(AttentionBackend):
         # (vllm_omni/distributed/omni_connectors/kv_transfer_manager.py:224-301)
         if block_size % 16 != 0:
             raise ValueError("B200 paged attention needs block_size % 16 == 0")
+        if cache_dtype_str == PER_TOKEN_HEAD:
+            # same byte budget as TritonAttentionBackend (triton_attn.py:312-334: one float32 scale per (slot, head) inline);
+            # the bytes of a block are laid out by ops.per_token_head_views (data pages first, scale runs behind them)
+            return (num_blocks, 2, block_size, num_kv_heads, head_size + 4)
         return (num_blocks, 2, block_size, num_kv_heads, head_size)
 
     @staticmethod
@@ -217,8 +222,12 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
         self._identity = torch.arange(self.max_rows, dtype=torch.int32, device=device)
         self.max_reqs = int(getattr(vllm_config.scheduler_config, "max_num_seqs", None) or self.max_rows)
         self._tile_prefix = torch.zeros(self.max_reqs + 1, dtype=torch.int32, device=device)
-        # the tensor-core prefill kernel reads the FP8 cache; 16-bit caches keep the per-token decode rows
-        self.use_prefill_kernel = self.kv_torch_dtype == torch.uint8 and self.head_dim == 128
+        # the tensor-core prefill kernel reads the FP8 cache with static scales; 16-bit caches and per-token-head scales keep the
+        # per-token decode rows
+        mode = getattr(kv_cache_spec, "kv_quant_mode", None)
+        self.per_token_head = bool(getattr(mode, "is_per_token_head", False)) or \
+            getattr(getattr(vllm_config, "cache_config", None), "cache_dtype", None) == PER_TOKEN_HEAD
+        self.use_prefill_kernel = self.kv_torch_dtype == torch.uint8 and self.head_dim == 128 and not self.per_token_head
         self._capturing = False
 
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
@@ -318,6 +327,17 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         self.logits_soft_cap = 0.0
         self.supports_quant_query_input = False   # Q stays bf16/fp16: K is expanded exactly in-kernel instead
         self._unit_scale: torch.Tensor | None = None
+        self.per_token_head = kv_cache_dtype == PER_TOKEN_HEAD
+        self._pth_views: dict = {}
+
+    def _per_token_head(self, kv_cache: torch.Tensor):
+        """(k, v, k_scale_cache, v_scale_cache) views of a per-token-head cache, built once per cache tensor."""
+        key = (kv_cache.data_ptr(), tuple(kv_cache.shape))
+        got = self._pth_views.get(key)
+        if got is None:
+            got = self._pth_views[key] = ops.per_token_head_views(kv_cache.view(torch.uint8) if kv_cache.dtype != torch.uint8 else kv_cache,
+                                                                  self.num_kv_heads, self.head_size)
+        return got
 
     # ---- helpers ----
     def _planes(self, kv_cache: torch.Tensor):
@@ -343,6 +363,13 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         slot_mapping may be longer than the real token count under padding: -1 entries are skipped in-kernel."""
         if self.kv_sharing_target_layer_name is not None:
             return   # the target layer already wrote this cache (attention.py:700-706 semantics)
+        if self.per_token_head:
+            k_cache, v_cache, ksc, vsc = self._per_token_head(kv_cache)
+            n = min(slot_mapping.shape[0], key.shape[0])
+            torch.ops.b200attn.kv_write_per_token_head(key[:n].view(n, self.num_kv_heads, self.head_size),
+                                                       value[:n].view(n, self.num_kv_heads, self.head_size), k_cache, v_cache, ksc, vsc,
+                                                       slot_mapping[:n])
+            return
         k_cache, v_cache = self._planes(kv_cache)
         k_scale, v_scale = self._scales(layer, key.device)
         n = min(slot_mapping.shape[0], key.shape[0])
@@ -354,7 +381,8 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
         """vLLM's RoPE+KV-cache fusion pass ($VLLM/compilation/passes/fusion/rope_kvcache_fusion.py:50) asks the impl; ours
         does both in one launch (csrc/rope_kv_write.cu).  KV-sharing layers keep the unfused path (they write no cache).
         The pass rewrites rotary_embedding + unified_kv_cache_update, an op that only exists under the two-op contract."""
-        return self.kv_sharing_target_layer_name is None and not B200PagedAttentionBackend.forward_includes_kv_cache_update
+        return (self.kv_sharing_target_layer_name is None and not self.per_token_head
+                and not B200PagedAttentionBackend.forward_includes_kv_cache_update)
 
     def do_rope_and_kv_cache_update(self, layer: AttentionLayer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
                                     positions: torch.Tensor, cos_sin_cache: torch.Tensor, is_neox: bool,
@@ -410,6 +438,20 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
             return output.fill_(0)    # profiling run (triton_attn.py:557-559)
         md = attn_metadata
         T = md.num_actual_tokens
+        if self.per_token_head:
+            # dynamic per-(token, head) scales: HMMA consumers with the scales applied to the logits / probabilities; every
+            # query token is a decode row (row_map), as for 16-bit caches
+            k_cache, v_cache, ksc, vsc = self._per_token_head(kv_cache)
+            q = query[:T].view(T, self.num_heads, self.head_size)
+            out = output[:T].view(T, self.num_heads, self.head_size)
+            if (B200PagedAttentionBackend.forward_includes_kv_cache_update and key is not None and value is not None
+                    and self.kv_sharing_target_layer_name is None):
+                torch.ops.b200attn.kv_write_per_token_head(key[:T].view(T, self.num_kv_heads, self.head_size),
+                                                           value[:T].view(T, self.num_kv_heads, self.head_size), k_cache, v_cache,
+                                                           ksc, vsc, md.slot_mapping[:T])
+            md.workspace.decode_per_token_head(q, k_cache, v_cache, ksc, vsc, md.block_table, md.seq_lens, out, self.scale,
+                                               row_map=md.row_map, fresh_tokens=max(1, md.max_query_len))
+            return output
         k_cache, v_cache = self._planes(kv_cache)
         k_scale, v_scale = self._scales(layer, query.device)
         q = query[:T].view(T, self.num_heads, self.head_size)

@@ -41,14 +41,18 @@ struct KvCfg {
 };
 
 // smem carve-up, shared by host (size) and device (offsets)
-template <int KVT, int NT>
+constexpr int kDynStageBytes = 2 * kTileTokens * 4;   // per stage: 64 K scales + 64 V scales (float32)
+constexpr int kDynMaxStages = 8;
+
+template <int KVT, int NT, bool DYN = false>
 struct Smem {
   static constexpr int kStageBytes = KvCfg<KVT>::kStageBytes;
+  static constexpr int kDynBytes = DYN ? kDynMaxStages * kDynStageBytes : 0;   // per-token scale ring (fp8_per_token_head)
   static constexpr int kRedOBytes = kConsumerWarps * NT * 8 * kRedStride * 4;
   static constexpr int kRedMlBytes = kConsumerWarps * kMaxGroup * 2 * 4;
   static constexpr int kDescBytes = 3 * 32;   // 2 segment descriptors + merge hand-off words
   static constexpr int kBarBytes = 256;
-  static constexpr int kFixedBytes = 2 * kQSlotBytes + kRedOBytes + kRedMlBytes + kDescBytes + kBarBytes;
+  static constexpr int kFixedBytes = 2 * kQSlotBytes + kRedOBytes + kRedMlBytes + kDescBytes + kBarBytes + kDynBytes;
   // fp8: 2 CTAs / SM (113 KiB, 6 x 16 KiB stages).  16-bit KV, G <= 8: also 2 CTAs / SM with 2 x 32 KiB stages each -- one CTA
   // per SM (6 stages) left the 4 consumer warps latency-bound at 75 % of HBM, two reach the copy peak (profiles/r01_sweep_*).
   // 16-bit KV with G > 8 (234 registers) stays at 1 CTA / SM.
@@ -61,11 +65,12 @@ struct Smem {
   static_assert(kTotalBytes <= kBudget, "smem budget exceeded");
 };
 
-template <int KVT, int QDT, int NT>
-__global__ void __launch_bounds__(kDecodeThreads, Smem<KVT, NT>::kCtas)
+template <int KVT, int QDT, int NT, bool DYN = false>
+__global__ void __launch_bounds__(kDecodeThreads, Smem<KVT, NT, DYN>::kCtas)
 decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v, const DecodeParams p) {
   using Cfg = KvCfg<KVT>;
-  using SM = Smem<KVT, NT>;
+  using SM = Smem<KVT, NT, DYN>;
+  static_assert(!DYN || Cfg::kFp8, "per-token scales belong to the fp8 cache");
   constexpr bool kFp8 = Cfg::kFp8;
   constexpr bool kMmaBf16 = !kFp8 && (KVT == B200ATTN_BF16);  // HMMA operand type (fp8 is expanded to f16)
   constexpr int kStages = SM::kStages;
@@ -80,6 +85,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
   const uint32_t redml_base = redo_base + SM::kRedOBytes;
   const uint32_t desc_base = redml_base + SM::kRedMlBytes;
   const uint32_t bar_base = desc_base + SM::kDescBytes;
+  const uint32_t dyn_base = bar_base + SM::kBarBytes;   // [stage][K | V][64 tokens] float32 (DYN only)
   // generic pointers for the small reduction buffers
   uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
   float* red_o = reinterpret_cast<float*>(smem_al + (redo_base - smem_base));
@@ -191,11 +197,20 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
         mbar_wait(empty_bar(stage), phase ^ 1);
         const int tok0 = tl * kTileTokens;
         const int nvalid = min(kConsumerWarps, (L - tok0 + kChunkTokens - 1) / kChunkTokens);
-        if (lane == 0) mbar_arrive_expect_tx(full_bar(stage), (uint32_t)nvalid * 2 * kChunkBytes);
+        if (lane == 0) mbar_arrive_expect_tx(full_bar(stage), (uint32_t)nvalid * 2 * (kChunkBytes + (DYN ? kChunkTokens * 4 : 0)));
         __syncwarp();
         const int c = (lane >> 1) & 3;
         const int kv = lane & 1;
         const int b = __shfl_sync(0xffffffffu, blk, ((tt & 7) << 2) + c);
+        if constexpr (DYN) {
+          // the chunk's 16 K scales and 16 V scales: 64 contiguous bytes each in the [block][head][slot] side caches
+          if (lane >= 8 && lane < 16 && c < nvalid) {
+            const int ci = (tl << 2) + c;
+            const int row0 = (ci % p.cpb) * kChunkTokens;
+            const float* src = (kv ? p.vs_cache : p.ks_cache) + (int64_t)b * p.sc_stride_block + (int64_t)kvh * p.sc_stride_head + row0;
+            bulk_load_1d(dyn_base + stage * kDynStageBytes + kv * (kTileTokens * 4) + c * (kChunkTokens * 4), src, kChunkTokens * 4, full_bar(stage));
+          }
+        }
         if (lane < 8 && c < nvalid) {
           const int ci = (tl << 2) + c;
           const int row0 = (ci % p.cpb) * kChunkTokens;
@@ -325,6 +340,20 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
         const uint32_t kbase = stages_base + stage * kStageBytes + w * kChunkBytes;
         const uint32_t vbase = kbase + kConsumerWarps * kChunkBytes;
         const bool partial = tok0 + kChunkTokens > L;
+        // per-token scales of tokens g and g + 8 of this warp's chunk; V's carry 2^6 so that p * scale stays clear of f16
+        // subnormals (undone by the constant v_scale = 2^-6 the host passes); positions past L must contribute exactly 0
+        float ks_lo = 1.f, ks_hi = 1.f, vs_lo = 0.f, vs_hi = 0.f;
+        if constexpr (DYN) {
+          const uint32_t sb0 = dyn_base + stage * kDynStageBytes + (w * kChunkTokens + g) * 4;
+          float a0, a1, b0, b1;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(a0) : "r"(sb0));
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(a1) : "r"(sb0 + 32));
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(b0) : "r"(sb0 + kTileTokens * 4));
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(b1) : "r"(sb0 + kTileTokens * 4 + 32));
+          ks_lo = a0; ks_hi = a1;
+          vs_lo = (tok0 + g < L) ? b0 * 64.0f : 0.f;
+          vs_hi = (tok0 + g + 8 < L) ? b1 * 64.0f : 0.f;
+        }
 
         // ---------------- S^T = K.Q^T : two accumulator chains (even / odd k-steps) per 8 heads ----------------
         float sa[NT][4], sb[NT][4];
@@ -374,6 +403,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
         for (int a = 0; a < NT; ++a) {
           float x0 = (sa[a][0] + sb[a][0]) * crow[a][0], x1 = (sa[a][1] + sb[a][1]) * crow[a][1];
           float x2 = (sa[a][2] + sb[a][2]) * crow[a][0], x3 = (sa[a][3] + sb[a][3]) * crow[a][1];
+          if constexpr (DYN) { x0 *= ks_lo; x1 *= ks_lo; x2 *= ks_hi; x3 *= ks_hi; }   // K's per-token scale (triton_unified_attention.py:506-510)
           if (partial) {
             if (tok0 + g >= L) { x0 = ninf; x1 = ninf; }
             if (tok0 + g + 8 >= L) { x2 = ninf; x3 = ninf; }
@@ -400,8 +430,13 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
           l_run[a][0] += p0 + p2;
           l_run[a][1] += p1 + p3;
           // [tok g][heads 2t,2t+1] --movmatrix.trans--> [head g][toks 2t,2t+1] = B fragment of P^T
-          pb[a][0] = movmatrix_trans(pack_f32x2<kMmaBf16>(p0, p1));
-          pb[a][1] = movmatrix_trans(pack_f32x2<kMmaBf16>(p2, p3));
+          if constexpr (DYN) {   // V's per-token scale rides on P (triton_unified_attention.py:540-543); l_run keeps the unscaled p
+            pb[a][0] = movmatrix_trans(pack_f32x2<kMmaBf16>(p0 * vs_lo, p1 * vs_lo));
+            pb[a][1] = movmatrix_trans(pack_f32x2<kMmaBf16>(p2 * vs_hi, p3 * vs_hi));
+          } else {
+            pb[a][0] = movmatrix_trans(pack_f32x2<kMmaBf16>(p0, p1));
+            pb[a][1] = movmatrix_trans(pack_f32x2<kMmaBf16>(p2, p3));
+          }
         }
 
         // ---------------- O^T(d x heads) += V^T(d x tok) . P^T(tok x heads) ----------------
@@ -560,10 +595,13 @@ int option_fused_write();
 int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, DecodeParams& p, int grid, int q_dtype, cudaStream_t stream);
 unsigned long long* option_debug_buffer();
 
-template <int KVT, int QDT, int NT>
+// constant scales of the per-token-head mode: K's logit factor is 1, V's output factor undoes the 2^6 carried on P
+__device__ float g_dyn_static_scales[2] = {1.0f, 1.0f / 64.0f};
+
+template <int KVT, int QDT, int NT, bool DYN = false>
 static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeParams& p, int grid, cudaStream_t stream) {
-  using SM = Smem<KVT, NT>;
-  auto fn = decode_kernel<KVT, QDT, NT>;
+  using SM = Smem<KVT, NT, DYN>;
+  auto fn = decode_kernel<KVT, QDT, NT, DYN>;
   static bool configured[64] = {};  // per instantiation and device (the attribute belongs to the context)
   int dev = 0;
   if (check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return B200ATTN_ECUDA;
@@ -586,6 +624,13 @@ int decode_smem_bytes(int kv_dtype, int nt) {
 
 using namespace b200attn;
 
+// per-(token, head) scale side caches (b200attn_decode_per_token_head)
+struct DynScales {
+  const float* ks_cache;
+  const float* vs_cache;
+  int64_t stride_block, stride_slot, stride_head;
+};
+
 // the new token of every row, for the decode launch that also writes the cache (b200attn_decode_kv_write)
 struct NewTokens {
   const void* key;
@@ -602,7 +647,7 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
                        float sm_scale, const float* k_scale, const float* v_scale, int32_t scale_stride,
                        const void* plan, int32_t num_ctas, void* workspace, size_t workspace_bytes,
                        float* lse_out, const int32_t* row_map, int32_t fresh_tokens, int32_t flags, void* stream,
-                       const NewTokens* nw) {
+                       const NewTokens* nw, const DynScales* dyn = nullptr) {
   if (num_seqs == 0) return B200ATTN_OK;
   if (!q || !out || !k_cache || !v_cache || !block_table || !seq_lens || !plan || !workspace) {
     set_error("decode: null pointer argument");
@@ -629,7 +674,7 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
     set_error("decode: 16-bit kv dtype (%d) must equal q dtype (%d)", kv_dtype, q_dtype);
     return B200ATTN_EINVAL;
   }
-  if (fp8 && (!k_scale || !v_scale)) {
+  if (fp8 && dyn == nullptr && (!k_scale || !v_scale)) {
     set_error("decode: fp8 cache needs k_scale / v_scale");
     return B200ATTN_EINVAL;
   }
@@ -689,8 +734,31 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
   p.kc_base = nullptr; p.vc_base = nullptr;
   p.c_stride_block = stride_block; p.c_stride_slot = stride_slot; p.c_stride_head = stride_head;
   p.block_size = block_size;
+  p.ks_cache = nullptr; p.vs_cache = nullptr; p.sc_stride_block = 0; p.sc_stride_head = 0;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dyn != nullptr) {
+    // fp8_per_token_head: the HMMA consumers apply K's scale to the logits and V's to P (decode.cu, DYN instantiation)
+    if (!fp8) {
+      set_error("decode_per_token_head: needs an fp8 cache");
+      return B200ATTN_EINVAL;
+    }
+    if (!dyn->ks_cache || !dyn->vs_cache || dyn->stride_slot != 1 || (dyn->stride_block % 4) || (dyn->stride_head % 4) ||
+        (reinterpret_cast<uintptr_t>(dyn->ks_cache) % 16) || (reinterpret_cast<uintptr_t>(dyn->vs_cache) % 16)) {
+      set_error("decode_per_token_head: scale caches must be 16-byte aligned float32 [block][head][slot] views (slot stride 1, "
+                "block / head strides multiples of 4)");
+      return B200ATTN_EINVAL;
+    }
+    float* cst = nullptr;
+    if (check_cuda(cudaGetSymbolAddress(reinterpret_cast<void**>(&cst), g_dyn_static_scales), "cudaGetSymbolAddress")) return B200ATTN_ECUDA;
+    p.k_scale = cst; p.v_scale = cst + 1; p.scale_stride = 0;
+    p.ks_cache = dyn->ks_cache; p.vs_cache = dyn->vs_cache;
+    p.sc_stride_block = dyn->stride_block; p.sc_stride_head = dyn->stride_head;
+    if (G > 8) return q_dtype == B200ATTN_BF16 ? launch_decode<B200ATTN_FP8_E4M3, B200ATTN_BF16, 2, true>(tk, tv, p, num_ctas, st)
+                                               : launch_decode<B200ATTN_FP8_E4M3, B200ATTN_FP16, 2, true>(tk, tv, p, num_ctas, st);
+    return q_dtype == B200ATTN_BF16 ? launch_decode<B200ATTN_FP8_E4M3, B200ATTN_BF16, 1, true>(tk, tv, p, num_ctas, st)
+                                    : launch_decode<B200ATTN_FP8_E4M3, B200ATTN_FP16, 1, true>(tk, tv, p, num_ctas, st);
+  }
   const bool use_tc = fp8 && G <= 8 && option_tc();
   if (nw != nullptr) {
     // In-kernel write: the tcgen05 kernel, rows == tokens (no row_map: with several query tokens per request a later row
@@ -762,4 +830,21 @@ extern "C" int b200attn_decode_kv_write(const void* q, int64_t q_stride_t, int64
                      stride_head, num_blocks, block_table, block_table_stride, seq_lens, num_seqs, num_q_heads, num_kv_heads,
                      head_dim, block_size, q_dtype, kv_dtype, sm_scale, k_scale, v_scale, scale_stride, plan, num_ctas, workspace,
                      workspace_bytes, lse_out, row_map, fresh_tokens, flags, stream, &nw);
+}
+
+extern "C" int b200attn_decode_per_token_head(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t,
+                                              int64_t out_stride_h, const void* k_cache, const void* v_cache, int64_t stride_block,
+                                              int64_t stride_slot, int64_t stride_head, int64_t num_blocks,
+                                              const float* k_scale_cache, const float* v_scale_cache, int64_t scale_stride_block,
+                                              int64_t scale_stride_slot, int64_t scale_stride_head, const int32_t* block_table,
+                                              int64_t block_table_stride, const int32_t* seq_lens, int32_t num_seqs,
+                                              int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                                              int32_t q_dtype, float sm_scale, const void* plan, int32_t num_ctas, void* workspace,
+                                              size_t workspace_bytes, float* lse_out, const int32_t* row_map, int32_t fresh_tokens,
+                                              int32_t flags, void* stream) {
+  DynScales dyn = {k_scale_cache, v_scale_cache, scale_stride_block, scale_stride_slot, scale_stride_head};
+  return decode_impl(q, q_stride_t, q_stride_h, out, out_stride_t, out_stride_h, k_cache, v_cache, stride_block, stride_slot,
+                     stride_head, num_blocks, block_table, block_table_stride, seq_lens, num_seqs, num_q_heads, num_kv_heads,
+                     head_dim, block_size, q_dtype, B200ATTN_FP8_E4M3, sm_scale, nullptr, nullptr, 0, plan, num_ctas, workspace,
+                     workspace_bytes, lse_out, row_map, fresh_tokens, flags, stream, nullptr, &dyn);
 }

@@ -41,6 +41,11 @@ struct DecodeParams {
   uint8_t* vc_base;
   int64_t c_stride_block, c_stride_slot, c_stride_head;   // elements (= bytes for the fp8 cache)
   int block_size;
+  // Per-(token, head) dynamic FP8 scales ("fp8_per_token_head"): float32 side caches [block][head][slot] (slot stride 1);
+  // nullptr = static per-tensor / per-head scales (k_scale / v_scale above)
+  const float* ks_cache;
+  const float* vs_cache;
+  int64_t sc_stride_block, sc_stride_head;   // float32 elements
   unsigned long long* dbg;  // debug timeline buffer [grid][16] (globaltimer ns) or nullptr
   int debug;            // bit0: consumers skip the math (pure streaming ceiling); never set in production
 };

@@ -157,3 +157,132 @@ extern "C" int b200attn_kv_write(const void* key, const void* value, int64_t key
   void* args[] = {&p};
   return launch_with_pdl(fn, dim3((unsigned)grid), dim3(block), 0, static_cast<cudaStream_t>(stream), args);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Per-(token, head) dynamic FP8 scales ("fp8_per_token_head").
+// Reference: _reshape_cache_per_token_head ($VLLM/v1/attention/ops/triton_reshape_and_cache_flash.py:138-236), one program
+// per (token, head):   scale = max(max|x| / 448, 1e-6);  byte = e4m3(clamp(x * (1 / scale), -448, 448));  scale stored in a
+// float32 side cache [num_blocks][block_size][Hkv] (any strides).  The two divisions are float32 `/` in Triton, which the
+// NVIDIA backend lowers to div.full.f32 (<= 2 ulp, not IEEE): B200ATTN_KV_DYN_IEEE_DIV selects div.rn instead (what numpy /
+// the Triton interpreter compute, and what the oracle's goldens pin); the default reproduces the compiled reference.
+// Mapping: a (token, K|V, head) row is handled by D/16 consecutive threads (16 elements each), the row's absmax is reduced
+// with warp shuffles (D/16 divides 32, rows are aligned to it), one thread stores the scale.
+// ------------------------------------------------------------------------------------------------
+namespace b200attn {
+
+struct KvWriteDynParams {
+  KvWriteParams w;          // k_scale / v_scale / scale_stride unused
+  float* k_scale_cache;
+  float* v_scale_cache;
+  int64_t sc_stride_block, sc_stride_slot, sc_stride_head;   // elements of float32
+  int ieee_div;
+};
+
+__device__ __forceinline__ float div_full(float a, float b) {
+  float r;
+  asm("div.full.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+
+template <int IN_DT>
+__global__ void __launch_bounds__(256) kv_write_dyn_kernel(const KvWriteDynParams q) {
+  const KvWriteParams& p = q.w;
+  const uint32_t lanes = (uint32_t)p.D >> 4;
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t row = gid / lanes;
+  const int col = (int)(gid - row * lanes) << 4;
+  const uint32_t rows = (uint32_t)p.T * 2 * p.Hkv;
+  pdl_launch_dependents();
+  pdl_wait();
+  const bool live = row < rows;   // nobody leaves before the shuffles
+  const int h = live ? (int)(row % p.Hkv) : 0;
+  const int kv = live ? (int)((row / p.Hkv) & 1) : 0;
+  const int t = live ? (int)(row / (2 * p.Hkv)) : 0;
+  using E = Elem<IN_DT>;
+  const typename E::type* src =
+      kv ? reinterpret_cast<const typename E::type*>(p.value) + (int64_t)t * p.value_stride_t + (int64_t)h * p.value_stride_h
+         : reinterpret_cast<const typename E::type*>(p.key) + (int64_t)t * p.key_stride_t + (int64_t)h * p.key_stride_h;
+  const int64_t slot = __ldg(p.slot_mapping + t);
+  float f[16];
+  if (live) {
+    const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(src + col));
+    const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(src + col + 8));
+    unpack8<IN_DT>(r0, *reinterpret_cast<float(*)[8]>(&f[0]));
+    unpack8<IN_DT>(r1, *reinterpret_cast<float(*)[8]>(&f[8]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) f[i] = 0.f;
+  }
+  float amax = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(f[i]));
+  for (uint32_t off = 1; off < lanes; off <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+  if (!live || slot < 0) return;
+  const float scale = fmaxf(q.ieee_div ? __fdiv_rn(amax, 448.0f) : div_full(amax, 448.0f), 1e-6f);
+  const float inv = q.ieee_div ? __fdiv_rn(1.0f, scale) : div_full(1.0f, scale);
+  const int64_t blk = slot / p.block_size;
+  const int64_t off = slot - blk * p.block_size;
+  if (col == 0) (kv ? q.v_scale_cache : q.k_scale_cache)[blk * q.sc_stride_block + off * q.sc_stride_slot + (int64_t)h * q.sc_stride_head] = scale;
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 lo = make_float2(fminf(fmaxf(f[4 * i + 0] * inv, -448.f), 448.f), fminf(fmaxf(f[4 * i + 1] * inv, -448.f), 448.f));
+    float2 hi = make_float2(fminf(fmaxf(f[4 * i + 2] * inv, -448.f), 448.f), fminf(fmaxf(f[4 * i + 3] * inv, -448.f), 448.f));
+    w[i] = (uint32_t)__nv_cvt_float2_to_fp8x2(lo, __NV_SATFINITE, __NV_E4M3) | ((uint32_t)__nv_cvt_float2_to_fp8x2(hi, __NV_SATFINITE, __NV_E4M3) << 16);
+  }
+  uint8_t* dst = reinterpret_cast<uint8_t*>(kv ? p.v_cache : p.k_cache) + blk * p.stride_block + off * p.stride_slot + (int64_t)h * p.stride_head + col;
+  *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+}  // namespace b200attn
+
+extern "C" int b200attn_kv_write_per_token_head(const void* key, const void* value, int64_t key_stride_t, int64_t key_stride_h,
+                                                int64_t value_stride_t, int64_t value_stride_h, void* k_cache, void* v_cache,
+                                                int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                                                float* k_scale_cache, float* v_scale_cache, int64_t scale_stride_block,
+                                                int64_t scale_stride_slot, int64_t scale_stride_head, const int64_t* slot_mapping,
+                                                int32_t num_tokens, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                                                int32_t in_dtype, int32_t flags, void* stream) {
+  if (num_tokens == 0) return B200ATTN_OK;
+  if (!key || !value || !k_cache || !v_cache || !slot_mapping || !k_scale_cache || !v_scale_cache) {
+    set_error("kv_write_per_token_head: null pointer argument");
+    return B200ATTN_EINVAL;
+  }
+  if (num_tokens < 0 || num_kv_heads <= 0 || block_size <= 0 || head_dim < 16 || head_dim > 512 || (head_dim & (head_dim - 1)) != 0) {
+    set_error("kv_write_per_token_head: bad shape T=%d Hkv=%d D=%d block_size=%d (D must be a power of two in 16..512)", num_tokens,
+              num_kv_heads, head_dim, block_size);
+    return B200ATTN_EINVAL;
+  }
+  if (in_dtype != B200ATTN_BF16 && in_dtype != B200ATTN_FP16) {
+    set_error("kv_write_per_token_head: key/value dtype must be bf16 or fp16 (got %d)", in_dtype);
+    return B200ATTN_EINVAL;
+  }
+  auto mis = [](const void* p, int64_t a) { return (reinterpret_cast<uintptr_t>(p) % a) != 0; };
+  if (mis(key, 16) || mis(value, 16) || mis(k_cache, 16) || mis(v_cache, 16) || mis(k_scale_cache, 4) || mis(v_scale_cache, 4) ||
+      (key_stride_t % 8) || (key_stride_h % 8) || (value_stride_t % 8) || (value_stride_h % 8) || (stride_block % 16) ||
+      (stride_slot % 16) || (stride_head % 16)) {
+    set_error("kv_write_per_token_head: pointers and strides must be 16-byte aligned");
+    return B200ATTN_EINVAL;
+  }
+  const int64_t threads = (int64_t)num_tokens * 2 * num_kv_heads * (head_dim / 16);
+  if (threads >= (1ll << 31)) {
+    set_error("kv_write_per_token_head: %lld work items exceed the 2^31 limit of one launch", (long long)threads);
+    return B200ATTN_EINVAL;
+  }
+  KvWriteDynParams q;
+  KvWriteParams& p = q.w;
+  p.key = key; p.value = value;
+  p.key_stride_t = key_stride_t; p.key_stride_h = key_stride_h;
+  p.value_stride_t = value_stride_t; p.value_stride_h = value_stride_h;
+  p.k_cache = k_cache; p.v_cache = v_cache;
+  p.stride_block = stride_block; p.stride_slot = stride_slot; p.stride_head = stride_head;
+  p.slot_mapping = slot_mapping; p.k_scale = nullptr; p.v_scale = nullptr; p.scale_stride = 0;
+  p.T = num_tokens; p.Hkv = num_kv_heads; p.D = head_dim; p.block_size = block_size;
+  q.k_scale_cache = k_scale_cache; q.v_scale_cache = v_scale_cache;
+  q.sc_stride_block = scale_stride_block; q.sc_stride_slot = scale_stride_slot; q.sc_stride_head = scale_stride_head;
+  q.ieee_div = (flags & B200ATTN_KV_DYN_IEEE_DIV) ? 1 : 0;
+  const int block = 256;
+  const void* fn = in_dtype == B200ATTN_BF16 ? (const void*)kv_write_dyn_kernel<B200ATTN_BF16> : (const void*)kv_write_dyn_kernel<B200ATTN_FP16>;
+  void* args[] = {&q};
+  return launch_with_pdl(fn, dim3((unsigned)((threads + block - 1) / block)), dim3(block), 0, static_cast<cudaStream_t>(stream), args);
+}

@@ -111,6 +111,106 @@ def _(key, value, k_cache, v_cache, slot_mapping, k_scale, v_scale) -> None:
 
 
 # ------------------------------------------------------------------------------------------------
+# fp8_per_token_head: dynamic per-(token, head) scales in float32 side caches
+# ------------------------------------------------------------------------------------------------
+def per_token_head_views(kv_cache: torch.Tensor, num_kv_heads: int, head_dim: int):
+    """The four views of a per-token-head cache allocation.  vLLM budgets, per block, 2*bs*Hkv*D bytes of e4m3 data plus
+    2*bs*Hkv float32 scales ($VLLM/v1/kv_cache_interface.py:150-163) and hands the backend `[nb, 2, bs, Hkv, D + 4]` bytes
+    (the shape TritonAttentionBackend.get_kv_cache_shape declares, triton_attn.py:312-334).  This backend lays a block out as
+        [K data: Hkv][bs][D] | [V data: Hkv][bs][D] | [K scales: Hkv][bs] f32 | [V scales: Hkv][bs] f32
+    so the data planes are the same HND pages as every other cache dtype (TMA boxes of 16 tokens x 128 bytes) and 16
+    consecutive tokens' scales are one 64-byte run.  Returns (k_cache, v_cache) uint8 `[nb, bs, Hkv, D]` and
+    (k_scale_cache, v_scale_cache) float32 `[nb, bs, Hkv]`, all views of `kv_cache`'s memory (any tensor whose blocks are
+    `2*bs*Hkv*(D+4)` contiguous bytes each, first dim = blocks)."""
+    if kv_cache.dim() != 5 or kv_cache.shape[1] != 2 or kv_cache.shape[3] != num_kv_heads or kv_cache.shape[4] != head_dim + 4 \
+            or kv_cache.element_size() != 1:
+        raise B200AttnError(f"per-token-head cache must be 1-byte [nb, 2, bs, Hkv, D + 4], got {tuple(kv_cache.shape)} {kv_cache.dtype}")
+    nb, _, bs, H, _ = kv_cache.shape
+    D = head_dim
+    blk = 2 * bs * H * (D + 4)
+    if kv_cache.stride(0) != blk:
+        raise B200AttnError("per-token-head cache: every block must be one contiguous run of 2*bs*Hkv*(D+4) bytes")
+    flat = torch.as_strided(kv_cache.view(torch.uint8), (nb * blk,), (1,), kv_cache.storage_offset())
+    k = torch.as_strided(flat, (nb, bs, H, D), (blk, D, bs * D, 1), flat.storage_offset())
+    v = torch.as_strided(flat, (nb, bs, H, D), (blk, D, bs * D, 1), flat.storage_offset() + H * bs * D)
+    f32 = flat.view(torch.float32)
+    so = 2 * H * bs * D // 4
+    ks = torch.as_strided(f32, (nb, bs, H), (blk // 4, 1, bs), f32.storage_offset() + so)
+    vs = torch.as_strided(f32, (nb, bs, H), (blk // 4, 1, bs), f32.storage_offset() + so + H * bs)
+    return k, v, ks, vs
+
+
+@torch.library.custom_op("b200attn::kv_write_per_token_head", mutates_args=("k_cache", "v_cache", "k_scale_cache", "v_scale_cache"),
+                         device_types="cuda")
+def kv_write_per_token_head(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                            k_scale_cache: torch.Tensor, v_scale_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                            ieee_div: bool = False) -> None:
+    """KV write with one dynamic scale per (token, head): scale = max(absmax / 448, 1e-6) into the float32 side caches
+    `[nb, bs, Hkv]` (any strides), bytes = e4m3(clamp(x / scale)).  `ieee_div`: IEEE divisions instead of the compiled
+    reference's div.full.f32 (include/b200attn.h)."""
+    _require_cuda(key, value, k_cache, v_cache, k_scale_cache, v_scale_cache, slot_mapping)
+    T = slot_mapping.shape[0]
+    if T == 0:
+        return
+    if key.dim() != 3 or value.shape != key.shape or key.stride(2) != 1 or value.stride(2) != 1:
+        raise B200AttnError("key/value must be [T, Hkv, D] with contiguous head_dim")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous():
+        raise B200AttnError("slot_mapping must be contiguous int64")
+    if _dt(k_cache) != DT_FP8_E4M3:
+        raise B200AttnError("per-token-head scales need an fp8 (1-byte) cache")
+    Hkv, D = key.shape[1], key.shape[2]
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    if k_scale_cache.dtype != torch.float32 or v_scale_cache.dtype != torch.float32 or k_scale_cache.shape != v_scale_cache.shape \
+            or k_scale_cache.stride() != v_scale_cache.stride() or tuple(k_scale_cache.shape) != (k_cache.shape[0], k_cache.shape[1], Hkv):
+        raise B200AttnError("scale caches must be float32 [num_blocks, block_size, Hkv] views with identical strides")
+    check(load_library().b200attn_kv_write_per_token_head(
+        key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1), value.stride(0), value.stride(1), k_cache.data_ptr(),
+        v_cache.data_ptr(), sb, ss, sh, k_scale_cache.data_ptr(), v_scale_cache.data_ptr(), k_scale_cache.stride(0),
+        k_scale_cache.stride(1), k_scale_cache.stride(2), slot_mapping.data_ptr(), T, Hkv, D, k_cache.shape[1], _dt(key),
+        1 if ieee_div else 0, _stream(key)), "b200attn_kv_write_per_token_head")
+
+
+@kv_write_per_token_head.register_fake
+def _(key, value, k_cache, v_cache, k_scale_cache, v_scale_cache, slot_mapping, ieee_div=False) -> None:
+    return None
+
+
+@torch.library.custom_op("b200attn::paged_decode_per_token_head", mutates_args=("out", "plan", "workspace", "lse"), device_types="cuda")
+def paged_decode_per_token_head(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, k_scale_cache: torch.Tensor,
+                                v_scale_cache: torch.Tensor, block_table: torch.Tensor, seq_lens: torch.Tensor, out: torch.Tensor,
+                                plan: torch.Tensor, workspace: torch.Tensor, sm_scale: float, num_ctas: int, lse: torch.Tensor,
+                                row_map: torch.Tensor, fresh_tokens: int = -1) -> None:
+    """paged_decode over a cache with per-(token, head) scales (b200attn_decode_per_token_head); the scale caches must have
+    slot stride 1 (`per_token_head_views`).  Split-KV partials are merged in-kernel."""
+    _require_cuda(query, k_cache, v_cache, k_scale_cache, v_scale_cache, block_table, seq_lens, out, plan, workspace)
+    if seq_lens.shape[0] == 0:
+        return
+    lse_ = lse if lse.numel() > 0 else None
+    rm = row_map if row_map.numel() > 0 else None
+    if query.dim() != 3 or out.dim() != 3 or query.stride(2) != 1 or out.stride(2) != 1 or query.dtype != out.dtype:
+        raise B200AttnError("query/out must be [B, Hq, D] of the same dtype with contiguous head_dim")
+    if block_table.dtype != torch.int32 or seq_lens.dtype != torch.int32 or block_table.stride(1) != 1:
+        raise B200AttnError("block_table / seq_lens must be int32 (block_table rows contiguous)")
+    if _dt(k_cache) != DT_FP8_E4M3 or k_scale_cache.dtype != torch.float32 or k_scale_cache.stride() != v_scale_cache.stride():
+        raise B200AttnError("per-token-head decode needs an fp8 cache and float32 scale caches with identical strides")
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    check(load_library().b200attn_decode_per_token_head(
+        query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), k_cache.data_ptr(),
+        v_cache.data_ptr(), sb, ss, sh, k_cache.shape[0], k_scale_cache.data_ptr(), v_scale_cache.data_ptr(), k_scale_cache.stride(0),
+        k_scale_cache.stride(1), k_scale_cache.stride(2), block_table.data_ptr(), block_table.stride(0), seq_lens.data_ptr(),
+        seq_lens.shape[0], query.shape[1], k_cache.shape[2], query.shape[2], k_cache.shape[1], _dt(query), float(sm_scale),
+        plan.data_ptr(), num_ctas, workspace.data_ptr(), workspace.numel() * 4, lse_.data_ptr() if lse_ is not None else None,
+        rm.data_ptr() if rm is not None else None, int(fresh_tokens), DECODE_FUSED_MERGE, _stream(query)),
+        "b200attn_decode_per_token_head")
+
+
+@paged_decode_per_token_head.register_fake
+def _(query, k_cache, v_cache, k_scale_cache, v_scale_cache, block_table, seq_lens, out, plan, workspace, sm_scale, num_ctas, lse,
+      row_map, fresh_tokens=-1) -> None:
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
 # rope_kv_write: rotary embedding of q / k in place + KV write, one launch (do_rope_and_kv_cache_update)
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("b200attn::rope_kv_write", mutates_args=("query", "key", "k_cache", "v_cache"), device_types="cuda")
@@ -496,6 +596,13 @@ class DecodeWorkspace:
                                                  self.plan, self.workspace, k_scale, v_scale, sm_scale, self.grid,
                                                  self._no_lse if lse is None else lse,
                                                  self._no_map if row_map is None else row_map, fresh_tokens, fused_merge)
+
+    def decode_per_token_head(self, query, k_cache, v_cache, k_scale_cache, v_scale_cache, block_table, seq_lens, out, sm_scale,
+                              lse=None, row_map=None, fresh_tokens: int = -1) -> None:
+        torch.ops.b200attn.paged_decode_per_token_head(query, k_cache, v_cache, k_scale_cache, v_scale_cache, block_table, seq_lens,
+                                                       out, self.plan, self.workspace, sm_scale, self.grid,
+                                                       self._no_lse if lse is None else lse,
+                                                       self._no_map if row_map is None else row_map, fresh_tokens)
 
     def decode(self, query, k_cache, v_cache, block_table, seq_lens, out, k_scale, v_scale, sm_scale, lse=None,
                row_map=None, fresh_tokens: int = -1, fused_merge: bool = True) -> None:

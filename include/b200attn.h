@@ -53,6 +53,8 @@ extern "C" {
 #define B200ATTN_ROPE_ROUND_EACH_OP 2  /* torch-native rounding of every elementary op (default: fp32, one rounding) */
 #define B200ATTN_ROPE_MROPE_INTERLEAVED 4 /* M-RoPE sections interleaved [THWTHW...TT] instead of chunked [T..H..W..] */
 
+#define B200ATTN_KV_DYN_IEEE_DIV 1 /* b200attn_kv_write_per_token_head: IEEE divisions instead of the compiled reference's div.full.f32 */
+
 #define B200ATTN_DECODE_FUSED_MERGE 1 /* merge split-KV partials inside the decode kernel (no b200attn_merge call) */
 
 /* geometry constants the host side needs */
@@ -89,6 +91,28 @@ B200ATTN_API int b200attn_kv_write(const void* key, const void* value,
                       int32_t in_dtype, int32_t kv_dtype,
                       const float* k_scale, const float* v_scale, int32_t scale_stride,
                       void* stream);
+
+/*
+ * Kernel 1 with per-(token, head) dynamic FP8 scales (kv_cache_dtype "fp8_per_token_head").
+ * Replaces: triton_reshape_and_cache_flash_per_token_head_quant
+ *   ($VLLM/v1/attention/ops/triton_reshape_and_cache_flash.py:138-300, called from TritonAttentionImpl.do_kv_cache_update,
+ *   $VLLM/v1/attention/backends/triton_attn.py:733-747).
+ * For every token t with slot >= 0 and every kv head h, for K and for V:
+ *   scale = max(max_d |x[t][h][d]| / 448, 1e-6);  cache byte = e4m3(clamp(x * (1 / scale), -448, 448));
+ *   scale_cache[slot / block_size][slot % block_size][h] = scale    (float32, strides in float32 elements).
+ * Both divisions are the compiled reference's div.full.f32 (bit-identical bytes and scales to the Triton kernel on the GPU);
+ * B200ATTN_KV_DYN_IEEE_DIV selects IEEE division (what numpy and the Triton interpreter compute).  head_dim: power of two.
+ */
+B200ATTN_API int b200attn_kv_write_per_token_head(const void* key, const void* value,
+                      int64_t key_stride_t, int64_t key_stride_h,
+                      int64_t value_stride_t, int64_t value_stride_h,
+                      void* k_cache, void* v_cache,
+                      int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                      float* k_scale_cache, float* v_scale_cache,
+                      int64_t scale_stride_block, int64_t scale_stride_slot, int64_t scale_stride_head,
+                      const int64_t* slot_mapping, int32_t num_tokens,
+                      int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                      int32_t in_dtype, int32_t flags, void* stream);
 
 /*
  * Kernel 1b -- fused rotary embedding + KV write (the step before the path).
@@ -253,6 +277,32 @@ B200ATTN_API int b200attn_decode_kv_write(const void* q, int64_t q_stride_t, int
                     float* lse_out /* nullable */,
                     const int32_t* row_map /* nullable */, int32_t fresh_tokens, int32_t flags,
                     void* stream);
+
+/*
+ * Kernel 2 over a cache with per-(token, head) dynamic FP8 scales (kv_cache_dtype "fp8_per_token_head").
+ * Replaces: kernel_unified_attention with KV_QUANT_MODE = FP8_PER_TOKEN_HEAD
+ *   ($VLLM/v1/attention/ops/triton_unified_attention.py:472-545: S = (Q.K8^T) * (scale * k_scale[token]),
+ *   acc += (P * v_scale[token]) . V8).
+ * k_scale_cache / v_scale_cache: float32 views [block][slot][head] of the side caches b200attn_kv_write_per_token_head
+ * fills, with slot stride 1 (the layout this library's backend allocates: 16 consecutive scales are one 64-byte copy),
+ * block / head strides in float32 elements.  fp8 cache only; every other argument as b200attn_decode (no static scales).
+ * The merge of split-KV partials is in-kernel (B200ATTN_DECODE_FUSED_MERGE) or by b200attn_merge with v_scale = NULL.
+ */
+B200ATTN_API int b200attn_decode_per_token_head(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+                    void* out, int64_t out_stride_t, int64_t out_stride_h,
+                    const void* k_cache, const void* v_cache,
+                    int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                    int64_t num_blocks,
+                    const float* k_scale_cache, const float* v_scale_cache,
+                    int64_t scale_stride_block, int64_t scale_stride_slot, int64_t scale_stride_head,
+                    const int32_t* block_table, int64_t block_table_stride,
+                    const int32_t* seq_lens, int32_t num_seqs,
+                    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                    int32_t block_size, int32_t q_dtype, float sm_scale,
+                    const void* plan, int32_t num_ctas,
+                    void* workspace, size_t workspace_bytes,
+                    float* lse_out /* nullable */, const int32_t* row_map /* nullable */,
+                    int32_t fresh_tokens, int32_t flags, void* stream);
 
 /*
  * Kernel 3 — merge of split-KV partials (online-softmax reduction with warp shuffles).

@@ -123,6 +123,32 @@ def kv_write_ref(key, value, k_cache, v_cache, slot_mapping, k_scale=None, v_sca
             v_cache[blk, off] = value[t]
 
 
+def kv_write_per_token_head_ref(key, value, k_cache, v_cache, k_scale_cache, v_scale_cache, slot_mapping):
+    """_reshape_cache_per_token_head ($VLLM/v1/attention/ops/triton_reshape_and_cache_flash.py:138-236), FP8 flavour
+    (QUANT_MAX 448): per (token, head)  scale = max(max|x| / 448, 1e-6) (:188, :214), stored in the float32 side cache
+    [nb, bs, Hkv] (:189-195), bytes = e4m3(clamp(x * (1 / scale), -448, 448)) (:197-206).  IEEE float32 arithmetic -- what
+    numpy and the Triton interpreter compute; the compiled Triton kernel's `/` is div.full.f32 (<= 2 ulp), which the CUDA
+    kernel reproduces by default and the on-box test pins against the compiled reference.  In place."""
+    bs = k_cache.shape[1]
+    for t, slot in enumerate(np.asarray(slot_mapping).tolist()):
+        if slot < 0:
+            continue
+        blk, off = slot // bs, slot % bs
+        for src, cache, sc in ((key, k_cache, k_scale_cache), (value, v_cache, v_scale_cache)):
+            x = np.asarray(src[t], dtype=np.float32)                                  # [Hkv, D]
+            scale = np.maximum(np.abs(x).max(axis=-1) / np.float32(448.0), np.float32(1e-6)).astype(np.float32)
+            sc[blk, off] = scale
+            inv = (np.float32(1.0) / scale).astype(np.float32)
+            cache[blk, off] = e4m3_encode_satfinite(np.clip((x * inv[:, None]).astype(np.float32), -448.0, 448.0))
+
+
+def dequant_per_token_head(cache_u8, scale_cache) -> np.ndarray:
+    """float32 [nb, bs, Hkv, D] = e4m3(byte) * scale[block, slot, head]: what kernel_unified_attention sees in
+    FP8_PER_TOKEN_HEAD mode (triton_unified_attention.py:472-545 applies k_scale[token] to S and v_scale[token] to P, which
+    is this product by linearity).  Feed it to paged_decode_exact(fp8=False) for the attention yardstick."""
+    return (e4m3_decode(cache_u8).astype(np.float32) * np.asarray(scale_cache, dtype=np.float32)[..., None]).astype(np.float32)
+
+
 # ------------------------------------------------------------------------------------------------
 # RoPE + KV write  (SURVEY.md 8(f) rank 1: AttentionImpl.do_rope_and_kv_cache_update, $VLLM/v1/attention/backend.py:815-840)
 # Unfused reference = RotaryEmbedding.forward ($VLLM/model_executor/layers/rotary_embedding/base.py:130-180,
