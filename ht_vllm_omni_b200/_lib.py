@@ -13,8 +13,8 @@ DT_BF16, DT_FP16, DT_FP8_E4M3 = 0, 1, 2
 TILE_TOKENS = 64
 MAX_GROUP = 16
 MAX_CTAS = 1024
-PEER_CTAS = 8
-ABI_VERSION = 6
+PEER_CTAS = 32
+ABI_VERSION = 7
 DECODE_FUSED_MERGE = 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -62,9 +62,9 @@ PROTOTYPES = {
     "b200attn_merge": (C.c_int, [_p, _i32, _p, _p, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p]),
     "b200attn_merge_lse": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
     "b200attn_merge_lse_peers": (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p]),
-    "b200attn_peer_gather_heads": (C.c_int, [_p, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i64, _p, _i64, _p, _i32, _i32, _p]),
-    "b200attn_peer_combine": (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _i32, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _i32, _p, _i64,
-                                        _i64, _p]),
+    "b200attn_peer_ll_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),
+    "b200attn_peer_gather_heads": (C.c_int, [_p, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _p]),
+    "b200attn_peer_combine": (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _i32, _i32, _p, _i64, _i64, _p]),
     "b200attn_prefill_tile_tokens": (C.c_int, [_i32, _i32]),
     "b200attn_prefill_plan": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p]),
     "b200attn_prefill": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _p, _p, _i32, _i32,

@@ -186,22 +186,24 @@ class PeerExchange:
 
 
 class PushExchange:
-    """The sequence-split exchange of a replica group as two PUSH launches per layer around the decode, no collective and no
-    barrier (csrc/peer_exchange.cu): `gather_q` replaces the all-gather of the group's query heads, `combine` the all-gather /
-    reduce-scatter of partials + merge (cp_lse_ag_out_rs, $VLLM/v1/attention/backends/flashinfer.py:1714-1738).
+    """The sequence-split exchange of a replica group as two PUSH launches per layer around the decode, no collective, no
+    barrier and no memory fence (csrc/peer_exchange.cu, "LL" words: every 8-byte store carries its own flag): `gather_q`
+    replaces the all-gather of the group's query heads, `combine` the all-gather / reduce-scatter of partials + merge
+    (cp_lse_ag_out_rs, $VLLM/v1/attention/backends/flashinfer.py:1714-1738).
 
         qg = px.gather_q(q_local)                       # [n, R * Hl, D]: every rank's heads, pushed by their owners
         o_part, lse_part = px.partial_buffers(n)        # hand these to the local decode (lse requested)
         ws.decode(qg, ..., o_part, ..., lse=lse_part)
         out = px.combine(n)                             # [n, Hl, D]: this rank's heads over the whole context
 
-    Every rank of the group must make the same calls with the same n.  Buffers are torch symmetric-memory allocations; flags
-    are launch counters, so the object is CUDA-graph safe (capture and replay see the same addresses, nothing is reset)."""
+    Every rank of the group must make the same calls with the same n.  Receive buffers are torch symmetric-memory
+    allocations; flags are launch counters, so the object is CUDA-graph safe (capture and replay see the same addresses,
+    nothing is reset)."""
 
     def __init__(self, max_rows: int, heads_local: int, head_dim: int, dtype: torch.dtype, device, group=None):
         import torch.distributed._symmetric_memory as symm_mem
 
-        from ._lib import PEER_CTAS
+        from ._lib import load_library
 
         self.group = group if group is not None else dist.group.WORLD
         self.R = dist.get_world_size(self.group)
@@ -209,22 +211,19 @@ class PushExchange:
         self.T, self.Hl, self.D, self.dtype = max_rows, heads_local, head_dim, dtype
         self.Hg = heads_local * self.R
         dev = torch.device(device)
-        self.gather = symm_mem.empty((2, max_rows, self.Hg, head_dim), dtype=dtype, device=dev)
-        self.recv_o = symm_mem.empty((2, self.R, max_rows, heads_local, head_dim), dtype=dtype, device=dev)
-        self.recv_lse = symm_mem.empty((2, self.R, max_rows, heads_local), dtype=torch.float32, device=dev)
-        self.flags = symm_mem.empty((2, self.R * PEER_CTAS), dtype=torch.int32, device=dev)   # [gather | combine]
-        self.flags.zero_()
-        self.h_gather = symm_mem.rendezvous(self.gather, self.group)
-        self.h_ro = symm_mem.rendezvous(self.recv_o, self.group)
-        self.h_rl = symm_mem.rendezvous(self.recv_lse, self.group)
-        self.h_flags = symm_mem.rendezvous(self.flags, self.group)
-        self.epoch = torch.zeros(2, PEER_CTAS, dtype=torch.int32, device=dev)
+        lib = load_library()
+        self.ll_q = symm_mem.empty((lib.b200attn_peer_ll_bytes(max_rows, heads_local, head_dim, self.R, 0) // 8,), dtype=torch.int64, device=dev)
+        self.ll_o = symm_mem.empty((lib.b200attn_peer_ll_bytes(max_rows, heads_local, head_dim, self.R, 1) // 8,), dtype=torch.int64, device=dev)
+        self.ll_q.zero_(); self.ll_o.zero_()
+        self.h_q = symm_mem.rendezvous(self.ll_q, self.group)
+        self.h_o = symm_mem.rendezvous(self.ll_o, self.group)
+        self.epoch = torch.zeros(2, 2, dtype=torch.int32, device=dev)
+        self.gathered = torch.zeros(2, max_rows, self.Hg, head_dim, dtype=dtype, device=dev)
         self.o_part = torch.zeros(max_rows, self.Hg, head_dim, dtype=dtype, device=dev)
         self.lse_part = torch.full((max_rows, self.Hg), float("-inf"), dtype=torch.float32, device=dev)
         self.slot = 0
-        self._flag_stride = self.R * PEER_CTAS
         torch.cuda.synchronize(dev)
-        dist.barrier(self.group)      # every rank's flag words are zero before anyone can push
+        dist.barrier(self.group)      # every rank's receive words are zero before anyone can push
 
     def _dt(self):
         from ._lib import DT_BF16, DT_FP16
@@ -232,19 +231,19 @@ class PushExchange:
         return DT_BF16 if self.dtype == torch.bfloat16 else DT_FP16
 
     def gather_q(self, q_local: torch.Tensor) -> torch.Tensor:
-        """q_local [n, Hl, D] (any token / head stride) -> the group's query heads [n, R * Hl, D] in this rank's buffer."""
+        """q_local [n, Hl, D] (any token / head stride) -> the group's query heads [n, R * Hl, D] in a local buffer."""
         from ._lib import check, load_library
 
         n = q_local.shape[0]
         if n > self.T or q_local.shape[1] != self.Hl or q_local.shape[2] != self.D or q_local.stride(2) != 1 or q_local.dtype != self.dtype:
             raise ValueError("q_local must be [n <= max_rows, heads_local, head_dim] of the exchange dtype")
-        self.slot ^= 1
+        self.slot ^= 1     # two local result buffers, so the caller may still read the previous step's queries
+        out = self.gathered[self.slot]
         stream = torch.cuda.current_stream(q_local.device)
         check(load_library().b200attn_peer_gather_heads(
-            q_local.data_ptr(), q_local.stride(0), q_local.stride(1), n, self.Hl, self.D, self._dt(), self.h_gather.buffer_ptrs_dev,
-            self.slot * self.T * self.Hg * self.D, self.h_flags.buffer_ptrs_dev, 0, self.epoch[0].data_ptr(), self.rank, self.R,
-            stream.cuda_stream), "b200attn_peer_gather_heads")
-        return self.gather[self.slot, :n]
+            q_local.data_ptr(), q_local.stride(0), q_local.stride(1), n, self.T, self.Hl, self.D, self._dt(), out.data_ptr(),
+            self.h_q.buffer_ptrs_dev, self.epoch[0].data_ptr(), self.rank, self.R, stream.cuda_stream), "b200attn_peer_gather_heads")
+        return out[:n]
 
     def partial_buffers(self, n: int) -> tuple[torch.Tensor, torch.Tensor]:
         return self.o_part[:n], self.lse_part[:n]
@@ -257,8 +256,7 @@ class PushExchange:
             out = torch.empty((n, self.Hl, self.D), dtype=self.dtype, device=dev)
         stream = torch.cuda.current_stream(dev)
         check(load_library().b200attn_peer_combine(
-            self.o_part.data_ptr(), self.lse_part.data_ptr(), n, self.T, self.Hl, self.D, self._dt(), self.h_ro.buffer_ptrs_dev,
-            self.R * self.T * self.Hl * self.D, self.h_rl.buffer_ptrs_dev, self.R * self.T * self.Hl, self.h_flags.buffer_ptrs_dev,
-            self._flag_stride, self.epoch[1].data_ptr(), self.rank, self.R, out.data_ptr(), out.stride(0), out.stride(1),
-            stream.cuda_stream), "b200attn_peer_combine")
+            self.o_part.data_ptr(), self.lse_part.data_ptr(), n, self.T, self.Hl, self.D, self._dt(), self.h_o.buffer_ptrs_dev,
+            self.epoch[1].data_ptr(), self.rank, self.R, out.data_ptr(), out.stride(0), out.stride(1), stream.cuda_stream),
+            "b200attn_peer_combine")
         return out

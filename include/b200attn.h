@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 6
+#define B200ATTN_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -60,7 +60,7 @@ extern "C" {
 /* geometry constants the host side needs */
 #define B200ATTN_TILE_TOKENS 64 /* scheduling granule of the split-KV decode kernel */
 #define B200ATTN_MAX_GROUP 16   /* query heads sharing one KV head handled per CTA */
-#define B200ATTN_PEER_CTAS 8    /* CTAs (= flag words and epoch counters per sender) of the peer-exchange kernels */
+#define B200ATTN_PEER_CTAS 32   /* CTAs of the peer-exchange kernels */
 
 B200ATTN_API int b200attn_abi_version(void);
 B200ATTN_API const char* b200attn_last_error(void);
@@ -344,39 +344,35 @@ B200ATTN_API int b200attn_merge_lse_peers(const void* const* parts_o_ptrs, const
 
 /*
  * Sequence-split exchange by PUSHES over NVLink peer memory (tp > Hkv: the ranks of a replica group share one KV head, each
- * holds 1/R of the context).  Two launches per layer around the decode, no collective, no barrier:
+ * holds 1/R of the context).  Two launches per layer around the decode; no collective, no barrier, no memory fence:
  *
- *   b200attn_peer_gather_heads   every rank stores its heads_local query heads into the gathered-query buffer
- *                                [n][R * heads_local][head_dim] of EVERY rank (slot = gather_offset elements in), raises a flag
- *                                at each peer and waits for the peers' flags: afterwards the local buffer holds the group's
- *                                query heads.  Replaces the all-gather of query heads of the DCP flow
- *                                ($VLLM/v1/attention/backends/flashinfer.py:1714-1738).
- *   b200attn_peer_combine        every rank stores, for each peer, the slice of its partial (o_part [n][R * heads_local][D],
- *                                lse_part [n][R * heads_local], natural log, -inf = empty) that covers THAT peer's heads into
- *                                the peer's receive buffer ([2 slots][R senders][rows_capacity][heads_local][D] and the same
- *                                without D for the LSE; the slot alternates by launch parity inside the kernel), raises the
- *                                flag, waits, and merges its own slice with the received ones by log-sum-exp into
- *                                out [n][heads_local][D].  Replaces cp_lse_ag_out_rs / merge_attn_states
+ *   b200attn_peer_gather_heads   every rank pushes its heads_local query heads to every peer and unpacks what the peers pushed:
+ *                                afterwards the LOCAL buffer `gathered` [n][R * heads_local][head_dim] holds the group's query
+ *                                heads (rank j's at heads [j * heads_local, (j + 1) * heads_local)).  Replaces the all-gather of
+ *                                query heads of the DCP flow ($VLLM/v1/attention/backends/flashinfer.py:1714-1738).
+ *   b200attn_peer_combine        every rank pushes, for each peer, the slice of its partial (o_part [n][R * heads_local][D],
+ *                                lse_part [n][R * heads_local], natural log, -inf = empty) that covers THAT peer's heads, and
+ *                                merges its own slice with the slices it receives by log-sum-exp into out [n][heads_local][D].
+ *                                Replaces cp_lse_ag_out_rs / merge_attn_states
  *                                ($VLLM/v1/attention/ops/merge_attn_states.py:7-101).
  *
- * gather_ptrs / recv_o_ptrs / recv_lse_ptrs / flag_ptrs are DEVICE arrays of num_ranks per-rank base pointers of symmetric
- * allocations (e.g. torch symmetric memory `buffer_ptrs_dev`).  Each op needs its own zero-initialised flag area of
- * num_ranks * B200ATTN_PEER_CTAS int32 per rank (at flag_offset elements) and its own LOCAL zero-initialised epoch counters
- * `epoch` [B200ATTN_PEER_CTAS] int32; flags carry launch counts, so nothing is ever reset and CUDA-graph replay is safe.
- * Every rank of the group must issue the same sequence of calls with the same n.  A peer that never arrives traps the
- * kernel after ~4 s instead of hanging the device.
+ * Transport: "LL" words -- each 8-byte store carries 4 payload bytes and the 4-byte launch count of the exchange; the receiver
+ * polls its LOCAL receive buffer until the count matches, so the data is its own flag.  `ll_ptrs` is a DEVICE array of
+ * num_ranks per-rank base pointers of a symmetric, ZERO-INITIALISED allocation (e.g. torch symmetric memory
+ * `buffer_ptrs_dev`) of b200attn_peer_ll_bytes(...) bytes per rank; each op needs its own allocation and its own LOCAL
+ * zero-initialised `epoch` words (2 x int32).  Nothing is ever reset, so CUDA-graph replay is safe.  Every rank of the group
+ * must issue the same sequence of calls with the same n.  A peer that never arrives traps the kernel after ~4 s instead of
+ * hanging the device.
  */
+B200ATTN_API size_t b200attn_peer_ll_bytes(int32_t rows_capacity, int32_t heads_local, int32_t head_dim, int32_t num_ranks,
+                              int32_t with_lse /* 0: gather_heads, 1: combine */);
 B200ATTN_API int b200attn_peer_gather_heads(const void* local, int64_t stride_t, int64_t stride_h, int32_t n,
-                               int32_t heads_local, int32_t head_dim, int32_t dtype,
-                               void* const* gather_ptrs, int64_t gather_offset,
-                               int32_t* const* flag_ptrs, int64_t flag_offset, int32_t* epoch,
+                               int32_t rows_capacity, int32_t heads_local, int32_t head_dim, int32_t dtype,
+                               void* gathered, void* const* ll_ptrs, int32_t* epoch,
                                int32_t rank, int32_t num_ranks, void* stream);
 B200ATTN_API int b200attn_peer_combine(const void* o_part, const float* lse_part, int32_t n, int32_t rows_capacity,
                           int32_t heads_local, int32_t head_dim, int32_t dtype,
-                          void* const* recv_o_ptrs, int64_t recv_o_slot_elems,
-                          float* const* recv_lse_ptrs, int64_t recv_lse_slot_elems,
-                          int32_t* const* flag_ptrs, int64_t flag_offset, int32_t* epoch,
-                          int32_t rank, int32_t num_ranks,
+                          void* const* ll_ptrs, int32_t* epoch, int32_t rank, int32_t num_ranks,
                           void* out, int64_t out_stride_t, int64_t out_stride_h, void* stream);
 
 /*

@@ -124,7 +124,7 @@ def layer_push():
 
 
 got3 = layer_push()
-assert torch.equal(pp.gather[pp.slot, :B].cpu(), q_all), "pushed query heads differ from the all-gathered ones"
+assert torch.equal(pp.gathered[pp.slot, :B].cpu(), q_all), "pushed query heads differ from the all-gathered ones"
 for _ in range(3):
     got3 = layer_push()
 torch.cuda.synchronize(); dist.barrier()
