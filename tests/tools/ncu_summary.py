@@ -36,7 +36,12 @@ def main():
             "sm__inst_executed_pipe_tensor.avg.pct_of_peak_sustained_active",
             "sm__inst_executed_pipe_uniform.avg.pct_of_peak_sustained_active",
             "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
-            "sm__cycles_elapsed.max", "smsp__inst_executed.sum"]
+            "sm__cycles_elapsed.max", "smsp__inst_executed.sum",
+            "lts__t_bytes.sum", "lts__t_sectors_srcunit_tex_op_read.sum", "l1tex__m_xbar2l1tex_read_bytes.sum",
+            "l1tex__m_xbar2l1tex_read_bytes.sum.per_second", "lts__t_bytes.sum.per_second",
+            "smsp__inst_executed_op_tma.sum", "sm__inst_executed_pipe_tma.sum", "l1tex__m_l1tex2xbar_write_bytes.sum",
+            "dram__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+            "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"]
     for w in want:
         if w in col:
             print(f"{w:75s} {r[col[w]]:>16s} {units[col[w]]}")
@@ -72,6 +77,8 @@ def main():
     print(f"\n## SASS opcode mix (warp instructions executed: {ninst})")
     for k, v in cnt.most_common(24):
         print(f"  {k:12s}{v:10d} {100 * v / max(ninst, 1):5.1f}%")
+    key = ["UTCQMMA", "UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UBLKCP", "SYNCS", "HMMA", "STAS", "MUFU", "F2FP"]
+    print("\n## tensor-core / TMEM / TMA instructions executed (warp instructions): " + ", ".join(f"{k} {cnt[k]}" for k in key if cnt.get(k)))
     print("\n## hottest instructions (samples, SASS, top stall reasons)")
     for x in sorted(body, key=lambda x: -int(x[ci["# Samples"]]))[:24]:
         st = {n[6:]: int(x[ci[n]]) for n in stalls if int(x[ci[n]]) > 0}
