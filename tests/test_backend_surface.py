@@ -130,6 +130,8 @@ def test_aligned_grid_policy():
     assert aligned_grid(296, 64, 16, 2) == 256      # c2: 128 pairs x 2
     assert aligned_grid(296, 32, 32, 4) == 256      # thinker B=32: 128 pairs x 2
     assert aligned_grid(296, 32, 16, 2) == 256      # 64 pairs x 4
+    assert aligned_grid(296, 32, 8, 1) == 256       # thinker at tp 4: 32 pairs x 8 (9 would cut clusters of 2 across pairs)
+    assert aligned_grid(296, 1, 8, 1) == 296        # one pair: 296 CTAs (already even)
     assert aligned_grid(296, 1, 16, 2) == 296       # 2 pairs x 148
     assert aligned_grid(296, 100, 16, 2) == 296     # 200 pairs: k = 1 -> default
     assert aligned_grid(296, 256, 16, 2) == 296     # more pairs than CTAs
