@@ -111,7 +111,9 @@ class B200PagedAttentionBackend(AttentionBackend):
 
     @classmethod
     def get_supported_head_sizes(cls) -> list[int]:
-        return [128]
+        # 128: the TMA / tcgen05 kernels; 64 and 256: the CUDA-core split-KV kernel (csrc/decode_simt.cu) -- the talker config
+        # class has no head_dim field, so class defaults resolve to hidden / heads = 64 (configuration_qwen3_tts.py:376-398)
+        return [64, 128, 256]
 
     @staticmethod
     def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int,
@@ -306,8 +308,10 @@ class B200PagedAttentionImpl(AttentionImpl[B200PagedAttentionMetadata]):
             raise NotImplementedError("B200 paged attention: attention sinks are not supported")
         if attn_type != AttentionType.DECODER:
             raise NotImplementedError("B200 paged attention: decoder self-attention only")
-        if head_size != 128:
-            raise NotImplementedError(f"B200 paged attention: head_size {head_size} unsupported (128 only)")
+        if head_size not in (64, 128, 256):
+            raise NotImplementedError(f"B200 paged attention: head_size {head_size} unsupported (64, 128 or 256)")
+        if kv_cache_dtype == PER_TOKEN_HEAD and head_size != 128:
+            raise NotImplementedError("B200 paged attention: fp8_per_token_head needs head_size 128")
         if getattr(self, "dcp_world_size", 1) > 1:   # set by AttentionImplBase.__new__ ($VLLM/v1/attention/backend.py:731-757)
             raise NotImplementedError("B200 paged attention: vLLM decode-context-parallel groups are not supported")
         if kv_cache_dtype not in B200PagedAttentionBackend.supported_kv_cache_dtypes:

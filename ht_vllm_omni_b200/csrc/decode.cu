@@ -593,6 +593,12 @@ int option_debug();
 int option_tc();
 int option_fused_write();
 int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, DecodeParams& p, int grid, int q_dtype, cudaStream_t stream);
+int launch_decode_simt(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t, int64_t out_stride_h,
+                       const void* k_cache, const void* v_cache, int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                       const int32_t* block_table, int64_t bt_stride, const int32_t* seq_lens, int B, int Hq, int Hkv, int D,
+                       int block_size, int q_dtype, int kv_dtype, float sm_scale, const float* k_scale, const float* v_scale,
+                       int scale_stride, int num_ctas, void* workspace, size_t workspace_bytes, float* lse_out,
+                       const int32_t* row_map, cudaStream_t st);
 unsigned long long* option_debug_buffer();
 
 // constant scales of the per-token-head mode: K's logit factor is 1, V's output factor undoes the 2^6 carried on P
@@ -653,10 +659,6 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
     set_error("decode: null pointer argument");
     return B200ATTN_EINVAL;
   }
-  if (head_dim != kD) {
-    set_error("decode: head_dim %d unsupported (only 128)", head_dim);
-    return B200ATTN_EINVAL;
-  }
   if (block_size <= 0 || block_size % kChunkTokens != 0 || block_size > 256) {
     set_error("decode: block_size %d must be a multiple of 16 and <= 256", block_size);
     return B200ATTN_EINVAL;
@@ -689,6 +691,32 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
     return B200ATTN_EINVAL;
   }
   const int G = Gfull / gsplit;
+  if (head_dim != kD) {
+    // head_dim 64 / 256: the CUDA-core kernel (decode_simt.cu); the tensor-core kernels tile 128-byte rows only
+    if (dyn != nullptr) {
+      set_error("decode_per_token_head: head_dim %d unsupported (only 128)", head_dim);
+      return B200ATTN_EINVAL;
+    }
+    if (fp8 && (!k_scale || !v_scale)) {
+      set_error("decode: fp8 cache needs k_scale / v_scale");
+      return B200ATTN_EINVAL;
+    }
+    if (Gfull > 64) {
+      set_error("decode: %d query heads per kv head unsupported", Gfull);
+      return B200ATTN_EINVAL;
+    }
+    if (nw != nullptr) {
+      int rcw = b200attn_kv_write(nw->key, nw->value, nw->key_stride_t, nw->key_stride_h, nw->value_stride_t, nw->value_stride_h,
+                                  const_cast<void*>(k_cache), const_cast<void*>(v_cache), stride_block, stride_slot, stride_head,
+                                  nw->slot_mapping, num_seqs, num_kv_heads, head_dim, block_size, q_dtype, kv_dtype, k_scale, v_scale,
+                                  scale_stride, stream);
+      if (rcw) return rcw;
+    }
+    return launch_decode_simt(q, q_stride_t, q_stride_h, out, out_stride_t, out_stride_h, k_cache, v_cache, stride_block, stride_slot,
+                              stride_head, block_table, block_table_stride, seq_lens, num_seqs, num_q_heads, num_kv_heads, head_dim,
+                              block_size, q_dtype, kv_dtype, sm_scale, k_scale, v_scale, scale_stride, num_ctas > 0 ? num_ctas : 1,
+                              workspace, workspace_bytes, lse_out, row_map, static_cast<cudaStream_t>(stream));
+  }
   if (num_ctas <= 0 || num_ctas > kMaxGrid) {
     set_error("decode: num_ctas %d out of range (1..%d)", num_ctas, kMaxGrid);
     return B200ATTN_EINVAL;

@@ -410,7 +410,9 @@ def paged_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tens
     # The in-kernel merge folds a pair's partials serially in ONE CTA: fine for the 2-4 partials of a large batch, slow when
     # a few long sequences are cut across the whole grid.  Past ~8 partials per (sequence, kv head) the merge kernel, which
     # spreads them over (pair, head) CTAs, follows instead.  Host-side shape arithmetic only (no device read).
-    if fused_merge and seq_lens.shape[0] * k_cache.shape[2] * 8 < num_ctas:
+    if query.shape[2] != 128:
+        fused_merge = True    # head_dim 64 / 256: the CUDA-core kernel folds its own splits (csrc/decode_simt.cu)
+    elif fused_merge and seq_lens.shape[0] * k_cache.shape[2] * 8 < num_ctas:
         fused_merge = False
     launch_split_decode(query, k_cache, v_cache, block_table, seq_lens, out, plan, workspace, k_scale, v_scale, sm_scale,
                         num_ctas, lse, row_map, fresh_tokens, fused_merge)
@@ -439,7 +441,9 @@ def paged_decode_kv_write(query: torch.Tensor, key: torch.Tensor, value: torch.T
         return
     lse = lse if lse.numel() > 0 else None
     row_map = row_map if row_map.numel() > 0 else None
-    if fused_merge and seq_lens.shape[0] * k_cache.shape[2] * 8 < num_ctas:
+    if query.shape[2] != 128:
+        fused_merge = True
+    elif fused_merge and seq_lens.shape[0] * k_cache.shape[2] * 8 < num_ctas:
         fused_merge = False
     launch_split_decode_kv_write(query, key, value, slot_mapping, k_cache, v_cache, block_table, seq_lens, out, plan, workspace,
                                  k_scale, v_scale, sm_scale, num_ctas, lse, row_map, fresh_tokens, fused_merge)

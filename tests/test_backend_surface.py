@@ -27,7 +27,7 @@ def test_backend_static_surface():
     assert sorted(be.get_kv_cache_stride_order(True)) == list(range(6))
     assert be.get_required_kv_cache_layout() == "HND"
     assert be.supports_block_size(16) and be.supports_block_size(128) and not be.supports_block_size(8)
-    assert be.supports_head_size(128) and not be.supports_head_size(64)
+    assert be.supports_head_size(128) and be.supports_head_size(64) and be.supports_head_size(256) and not be.supports_head_size(96)
     assert be.supports_kv_cache_dtype("fp8") and be.supports_kv_cache_dtype("fp8_e4m3") and not be.supports_kv_cache_dtype("fp8_e5m2")
     assert be.supports_per_head_quant_scales()
     with pytest.raises(ValueError):
@@ -46,7 +46,7 @@ def _validate(**over):
 def test_validate_configuration_returns_reasons_not_exceptions():
     assert _validate() == []
     assert _validate(kv_cache_dtype="bfloat16") == []
-    assert any("head_size" in r for r in _validate(head_size=64))
+    assert any("head_size" in r for r in _validate(head_size=96))
     assert any("kv_cache_dtype" in r for r in _validate(kv_cache_dtype="fp8_e5m2"))
     assert any("block_size" in r for r in _validate(block_size=8))
     assert any("compute capability" in r for r in _validate(device_capability=types.SimpleNamespace(major=9, minor=0)))
@@ -107,7 +107,7 @@ def test_impl_rejects_unsupported_features_at_construction():
         with pytest.raises(NotImplementedError):
             Impl(**args)
     with pytest.raises(NotImplementedError):
-        Impl(16, 64, 0.1, 2)
+        Impl(16, 96, 0.1, 2)
 
 
 def test_impl_profile_run_and_no_cpu_fallback():
