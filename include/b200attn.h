@@ -219,9 +219,10 @@ B200ATTN_API size_t b200attn_workspace_bytes(int32_t head_dim, int32_t num_ctas)
  * inside one CTA are written to `out` directly; the others leave (o, m, l) partials in `workspace`.  With
  * B200ATTN_DECODE_FUSED_MERGE the last CTA to deliver a partial of a pair reduces them in-kernel (arrival
  * counters live in the plan buffer); without it b200attn_merge must follow.
- * q/out dtype = q_dtype; kv_dtype fp8 accepts either q dtype, 16-bit KV must equal q_dtype.  head_dim must be
- * 128; block_size a multiple of 16.  The K/V planes are read through TMA: base pointers and byte strides
- * must be 16-byte aligned.
+ * q/out dtype = q_dtype; kv_dtype fp8 accepts either q dtype, 16-bit KV must equal q_dtype.  head_dim 128 runs the
+ * tensor-core kernels (K/V planes read through TMA); head_dim 64 and 256 run a CUDA-core split-KV kernel that ignores the
+ * plan and folds its own partials in `workspace` (decode_simt.cu).  block_size a multiple of 16; base pointers and byte
+ * strides 16-byte aligned.
  * fresh_tokens: upper bound on how many TRAILING positions of any row the kernel launched immediately before
  * this one on `stream` may have written (1 for a decode step's KV write, max_query_len in general); K/V tiles
  * below seq_len - fresh_tokens are prefetched before the programmatic-dependent-launch wait.  Pass -1 when
