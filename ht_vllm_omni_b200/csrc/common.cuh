@@ -282,6 +282,28 @@ struct Elem<B200ATTN_FP16> {
   static __device__ __forceinline__ type from_float(float v) { return __float2half_rn(v); }
 };
 
+// Division of a 32-bit index by a launch-constant divisor without the integer-divide sequence (which goes through the XU
+// pipe: ~20 instructions per quotient; the element-wise kernels did three per 16 bytes, profiles/r01_ncu_rope_kv_write_v8.txt
+// 33 % pipe_xu).  Granlund-Montgomery round-up method, exact for every 32-bit n: for d = 2^k a shift, otherwise
+//   L = ceil(log2 d), m = floor(2^32 (2^L - d) / d) + 1,  q = (t + ((n - t) >> 1)) >> (L - 1)  with  t = umulhi(m, n).
+struct FastDiv {
+  uint32_t d, m, s;   // s = L - 1 (or log2 d for powers of two, with m = 0)
+  __host__ void init(uint32_t div) {
+    d = div ? div : 1;
+    uint32_t L = 0;
+    while ((1ull << L) < d) ++L;
+    if ((1ull << L) == d) { m = 0; s = L; return; }
+    m = (uint32_t)(((1ull << 32) * ((1ull << L) - d)) / d + 1);
+    s = L - 1;
+  }
+  __device__ __forceinline__ uint32_t div(uint32_t n) const {
+    if (m == 0) return n >> s;
+    const uint32_t t = __umulhi(m, n);
+    return (t + ((n - t) >> 1)) >> s;
+  }
+  __device__ __forceinline__ void divmod(uint32_t n, uint32_t& q, uint32_t& r) const { q = div(n); r = n - q * d; }
+};
+
 // host-side error plumbing (abi.cu)
 void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);

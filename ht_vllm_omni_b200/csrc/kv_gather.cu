@@ -23,6 +23,7 @@ struct KvGatherParams {
   const int32_t* block_ids;
   uint8_t* out;                  // [num_layers][2][n_tokens][Hkv][row_bytes]
   int num_layers, n_tokens, Hkv, block_size, row_bytes;
+  FastDiv d_vec, d_heads, d_bs;   // vectors per row, kv heads, block size
 };
 
 __global__ void __launch_bounds__(256) kv_gather_kernel(const KvGatherParams p) {
@@ -34,14 +35,12 @@ __global__ void __launch_bounds__(256) kv_gather_kernel(const KvGatherParams p) 
   const uint32_t per_plane = (uint32_t)p.n_tokens * p.Hkv * vec_per_row;
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= per_plane) return;
-  const uint32_t rowi = idx / vec_per_row;
-  const uint32_t c = idx - rowi * vec_per_row;
-  const uint32_t tok = rowi / p.Hkv;
-  const uint32_t h = rowi - tok * p.Hkv;
+  uint32_t rowi, c, tok, h, bi, slot;
+  p.d_vec.divmod(idx, rowi, c);
+  p.d_heads.divmod(rowi, tok, h);
   const uint32_t kv = blockIdx.y & 1, layer = blockIdx.y >> 1;
-  const uint32_t bi = tok / p.block_size;
+  p.d_bs.divmod(tok, bi, slot);
   const int32_t blk = __ldg(p.block_ids + bi);
-  const uint32_t slot = tok - bi * p.block_size;
   uint4 v = make_uint4(0u, 0u, 0u, 0u);
   if (blk >= 0 && blk < p.num_blocks) {
     const uint8_t* base = reinterpret_cast<const uint8_t*>(kv ? p.v_planes[layer] : p.k_planes[layer]);
@@ -80,6 +79,7 @@ extern "C" int b200attn_kv_gather(const void* const* k_planes, const void* const
   p.stride_block = stride_block_bytes; p.stride_slot = stride_slot_bytes; p.stride_head = stride_head_bytes;
   p.num_blocks = num_blocks; p.block_ids = block_ids; p.out = reinterpret_cast<uint8_t*>(out);
   p.num_layers = num_layers; p.n_tokens = n_tokens; p.Hkv = num_kv_heads; p.block_size = block_size; p.row_bytes = row_bytes;
+  p.d_vec.init((uint32_t)row_bytes / 16); p.d_heads.init((uint32_t)num_kv_heads); p.d_bs.init((uint32_t)block_size);
   const int64_t per_plane = (int64_t)n_tokens * num_kv_heads * (row_bytes / 16);
   const int64_t gx = (per_plane + 255) / 256;
   if (per_plane >= (1ll << 32) || gx >= (1ll << 31) || 2ll * num_layers > 65535) {

@@ -25,6 +25,7 @@ struct KvWriteParams {
   const float* v_scale;
   int scale_stride;
   int T, Hkv, D, block_size;
+  FastDiv d_lanes, d_heads, d_bs;   // threads per row (D / 16), kv heads, block size
 };
 
 template <int IN_DT>
@@ -46,20 +47,21 @@ __device__ __forceinline__ uint32_t quant4(const float* f, float scale) {
 
 template <int IN_DT, bool FP8>
 __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
-  const int lanes_per_row = p.D >> 4;
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t row = gid / lanes_per_row;
-  const int col = (int)(gid - row * lanes_per_row) << 4;
-  const int64_t rows = (int64_t)p.T * 2 * p.Hkv;
+  // 32-bit index math with multiply-shift divisions (the host rejects launches with >= 2^31 threads)
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t row, lane_in_row;
+  p.d_lanes.divmod(gid, row, lane_in_row);
+  const int col = (int)lane_in_row << 4;
+  const uint32_t rows = (uint32_t)p.T * 2 * p.Hkv;
   // Dependent launch: let the decode kernel that follows become resident right away (it prefetches K/V tiles that
   // this kernel cannot touch and only then waits for us); everything above is index math, wait for the producer of
   // key/value here.
   pdl_launch_dependents();
   pdl_wait();
   if (row >= rows) return;
-  const int h = (int)(row % p.Hkv);
-  const int kv = (int)((row / p.Hkv) & 1);
-  const int t = (int)(row / (2 * p.Hkv));
+  uint32_t tkv, hh;
+  p.d_heads.divmod(row, tkv, hh);
+  const int h = (int)hh, kv = (int)(tkv & 1), t = (int)(tkv >> 1);
   // the slot, the two data vectors and the scale are independent loads: issue them together (one memory round trip on the
   // critical path between two decode kernels instead of two); a padding token's key/value row exists, reading it is harmless
   using E = Elem<IN_DT>;
@@ -72,8 +74,9 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteParams p) {
   float scale = 1.0f;
   if constexpr (FP8) scale = __ldg((kv ? p.v_scale : p.k_scale) + (int64_t)h * p.scale_stride);
   if (slot < 0) return;  // padding token
-  const int64_t blk = slot / p.block_size;
-  const int64_t off = slot - blk * p.block_size;
+  uint32_t blk32, off32;
+  p.d_bs.divmod((uint32_t)slot, blk32, off32);   // slots are < num_blocks * block_size < 2^32
+  const int64_t blk = blk32, off = off32;
   const int64_t dst_off = blk * p.stride_block + off * p.stride_slot + (int64_t)h * p.stride_head + col;
 
   if constexpr (FP8) {
@@ -145,8 +148,13 @@ extern "C" int b200attn_kv_write(const void* key, const void* value, int64_t key
   p.stride_block = stride_block; p.stride_slot = stride_slot; p.stride_head = stride_head;
   p.slot_mapping = slot_mapping; p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;
   p.T = num_tokens; p.Hkv = num_kv_heads; p.D = head_dim; p.block_size = block_size;
+  p.d_lanes.init((uint32_t)head_dim / 16); p.d_heads.init((uint32_t)num_kv_heads); p.d_bs.init((uint32_t)block_size);
 
   const int64_t threads = (int64_t)num_tokens * 2 * num_kv_heads * (head_dim / 16);
+  if (threads >= (1ll << 31)) {
+    set_error("kv_write: %lld work items exceed the 2^31 limit of one launch; split the token range", (long long)threads);
+    return B200ATTN_EINVAL;
+  }
   const int block = 256;
   const int64_t grid = (threads + block - 1) / block;
   const void* fn;
@@ -189,15 +197,16 @@ __global__ void __launch_bounds__(256) kv_write_dyn_kernel(const KvWriteDynParam
   const KvWriteParams& p = q.w;
   const uint32_t lanes = (uint32_t)p.D >> 4;
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t row = gid / lanes;
-  const int col = (int)(gid - row * lanes) << 4;
+  uint32_t row, lane_in_row;
+  p.d_lanes.divmod(gid, row, lane_in_row);
+  const int col = (int)lane_in_row << 4;
   const uint32_t rows = (uint32_t)p.T * 2 * p.Hkv;
   pdl_launch_dependents();
   pdl_wait();
   const bool live = row < rows;   // nobody leaves before the shuffles
-  const int h = live ? (int)(row % p.Hkv) : 0;
-  const int kv = live ? (int)((row / p.Hkv) & 1) : 0;
-  const int t = live ? (int)(row / (2 * p.Hkv)) : 0;
+  uint32_t tkv, hh;
+  p.d_heads.divmod(live ? row : 0u, tkv, hh);
+  const int h = (int)hh, kv = (int)(tkv & 1), t = (int)(tkv >> 1);
   using E = Elem<IN_DT>;
   const typename E::type* src =
       kv ? reinterpret_cast<const typename E::type*>(p.value) + (int64_t)t * p.value_stride_t + (int64_t)h * p.value_stride_h
@@ -220,8 +229,9 @@ __global__ void __launch_bounds__(256) kv_write_dyn_kernel(const KvWriteDynParam
   if (!live || slot < 0) return;
   const float scale = fmaxf(q.ieee_div ? __fdiv_rn(amax, 448.0f) : div_full(amax, 448.0f), 1e-6f);
   const float inv = q.ieee_div ? __fdiv_rn(1.0f, scale) : div_full(1.0f, scale);
-  const int64_t blk = slot / p.block_size;
-  const int64_t off = slot - blk * p.block_size;
+  uint32_t blk32, off32;
+  p.d_bs.divmod((uint32_t)slot, blk32, off32);
+  const int64_t blk = blk32, off = off32;
   if (col == 0) (kv ? q.v_scale_cache : q.k_scale_cache)[blk * q.sc_stride_block + off * q.sc_stride_slot + (int64_t)h * q.sc_stride_head] = scale;
   uint32_t w[4];
 #pragma unroll
@@ -278,6 +288,7 @@ extern "C" int b200attn_kv_write_per_token_head(const void* key, const void* val
   p.stride_block = stride_block; p.stride_slot = stride_slot; p.stride_head = stride_head;
   p.slot_mapping = slot_mapping; p.k_scale = nullptr; p.v_scale = nullptr; p.scale_stride = 0;
   p.T = num_tokens; p.Hkv = num_kv_heads; p.D = head_dim; p.block_size = block_size;
+  p.d_lanes.init((uint32_t)head_dim / 16); p.d_heads.init((uint32_t)num_kv_heads); p.d_bs.init((uint32_t)block_size);
   q.k_scale_cache = k_scale_cache; q.v_scale_cache = v_scale_cache;
   q.sc_stride_block = scale_stride_block; q.sc_stride_slot = scale_stride_slot; q.sc_stride_head = scale_stride_head;
   q.ieee_div = (flags & B200ATTN_KV_DYN_IEEE_DIV) ? 1 : 0;

@@ -40,6 +40,7 @@ struct RopeKvParams {
   const float* v_scale;
   int scale_stride;
   int T, Hq, Hkv, D, rot, block_size, is_neox, each_op;
+  FastDiv d_lanes, d_units, d_bs;         // threads per row (D / 16), heads per token (Hq + 2 Hkv), block size
   int sec_t, sec_h, sec_w, interleaved;   // M-RoPE sections (frequency counts per axis, sum = rot / 2); all 0 = plain RoPE
 };
 
@@ -107,24 +108,28 @@ __device__ __forceinline__ int mrope_axis(const RopeKvParams& p, int f) {
   return f < p.sec_t ? 0 : (f < p.sec_t + p.sec_h ? 1 : 2);
 }
 
-template <int DT, bool FP8>
-__global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p) {
+// EXT = the launch uses the fused RMSNorm and / or M-RoPE stages; the plain instantiation carries none of their code (48
+// registers and 5 resident CTAs per SM instead of 74 and 3, which costs 60 % of the throughput at prefill sizes).
+template <int DT, bool FP8, bool EXT>
+__global__ void __launch_bounds__(256, EXT ? 4 : 5) rope_kv_write_kernel(const RopeKvParams p) {
   using E = Elem<DT>;
   // 32-bit index math (the host rejects launches with >= 2^31 threads): 64-bit divisions would cost more than the rotation
   const uint32_t lanes = (uint32_t)p.D >> 4;
   const uint32_t units = (uint32_t)(p.Hq + 2 * p.Hkv);
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t row = gid / lanes;
-  const int j = (int)(gid - row * lanes);
+  uint32_t row, ju;
+  p.d_lanes.divmod(gid, row, ju);
+  const int j = (int)ju;
   pdl_launch_dependents();
   pdl_wait();
   // With a fused RMSNorm the D/16 threads of a row reduce its sum of squares by warp shuffles (D/16 divides 32 and rows are
   // aligned to it), so no thread may leave before that point; without it the early exits below are taken as before.
-  const bool any_norm = p.q_norm_w != nullptr || p.k_norm_w != nullptr;
+  const bool any_norm = EXT && (p.q_norm_w != nullptr || p.k_norm_w != nullptr);
   bool live = row < (uint32_t)p.T * units;
   if (!any_norm && !live) return;
-  const int t = live ? (int)(row / units) : 0;
-  const int u = live ? (int)(row - (uint32_t)t * units) : 0;
+  uint32_t tu, uu;
+  p.d_units.divmod(live ? row : 0u, tu, uu);
+  const int t = (int)tu, u = (int)uu;
   const int kind = u < p.Hq ? 0 : (u < p.Hq + p.Hkv ? 1 : 2);   // q, k, v
   const int h = kind == 0 ? u : (kind == 1 ? u - p.Hq : u - p.Hq - p.Hkv);
   // slot, position and the data vectors are independent loads, issued together (see kv_write.cu)
@@ -133,7 +138,7 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
 
   const int half = p.rot >> 1;
   const bool rotary = kind != 2 && j < (p.rot >> 4);
-  const void* norm_w = kind == 0 ? p.q_norm_w : (kind == 1 ? p.k_norm_w : nullptr);
+  const void* norm_w = !EXT ? nullptr : (kind == 0 ? p.q_norm_w : (kind == 1 ? p.k_norm_w : nullptr));
   int a0, a1;
   if (rotary && p.is_neox) { a0 = 8 * j; a1 = half + 8 * j; }
   else if (rotary) { a0 = 16 * j; a1 = a0 + 8; }
@@ -156,7 +161,7 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
   if (kind == 2 && slot < 0) live = false;   // padding token: nothing to write
   if (!any_norm && !live) return;
 
-  if (any_norm) {
+  if constexpr (EXT) if (any_norm) {
     // ---- RMSNorm over the head ($VLLM/model_executor/layers/layernorm.py forward_native / csrc/layernorm_kernels.cu):
     //   y = rnd(rnd(x * rsqrt(mean(x^2) + eps)) * w)   -- fp32 statistics, the normalised value rounded to the activation
     // dtype BEFORE the multiplication by the weight, which is itself a 16-bit multiply (one more rounding)
@@ -182,10 +187,10 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
 
   if (rotary) {
     float cs[8], sn[8];
-    if (p.pos_axis_stride == 0) {
+    if (!EXT || p.pos_axis_stride == 0) {
       load8<DT>(p.cos_sin, pos * p.rot + 8 * j, cs);
       load8<DT>(p.cos_sin, pos * p.rot + half + 8 * j, sn);
-    } else {
+    } else if constexpr (EXT) {
       // M-RoPE: frequency f takes cos / sin from the cache row of ITS axis' position; a chunk of 8 frequencies can touch all
       // three rows (interleaved layout), each fetched only when one of its frequencies needs it
       int ax[8];
@@ -233,8 +238,9 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
   }
   if (kind == 0 || slot < 0) return;
 
-  const int64_t blk = slot / p.block_size;
-  const int64_t off = slot - blk * p.block_size;
+  uint32_t blk32, off32;
+  p.d_bs.divmod((uint32_t)slot, blk32, off32);   // slots are < num_blocks * block_size < 2^32
+  const int64_t blk = blk32, off = off32;
   const int64_t dst_off = blk * p.stride_block + off * p.stride_slot + (int64_t)h * p.stride_head;
   if constexpr (FP8) {
     const float scale = __ldg((kind == 1 ? p.k_scale : p.v_scale) + (int64_t)h * p.scale_stride);
@@ -332,6 +338,7 @@ static int rope_impl(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_
   p.slot_mapping = slot_mapping; p.k_scale = k_scale; p.v_scale = v_scale; p.scale_stride = scale_stride;
   p.T = num_tokens; p.Hq = num_q_heads; p.Hkv = num_kv_heads; p.D = head_dim; p.rot = rotary_dim;
   p.block_size = block_size;
+  p.d_lanes.init((uint32_t)head_dim / 16); p.d_units.init((uint32_t)(num_q_heads + 2 * num_kv_heads)); p.d_bs.init((uint32_t)block_size);
   p.is_neox = (rope_flags & B200ATTN_ROPE_NEOX) ? 1 : 0;
   p.each_op = (rope_flags & B200ATTN_ROPE_ROUND_EACH_OP) ? 1 : 0;
 
@@ -343,10 +350,13 @@ static int rope_impl(void* query, int64_t q_stride_t, int64_t q_stride_h, int32_
     return B200ATTN_EINVAL;
   }
   const void* fn;
+  const bool ext = q_norm_weight != nullptr || k_norm_weight != nullptr || positions_axis_stride != 0;
+#define B200_ROPE_FN(DT, F8) (ext ? (const void*)rope_kv_write_kernel<DT, F8, true> : (const void*)rope_kv_write_kernel<DT, F8, false>)
   if (fp8)
-    fn = in_dtype == B200ATTN_BF16 ? (const void*)rope_kv_write_kernel<B200ATTN_BF16, true> : (const void*)rope_kv_write_kernel<B200ATTN_FP16, true>;
+    fn = in_dtype == B200ATTN_BF16 ? B200_ROPE_FN(B200ATTN_BF16, true) : B200_ROPE_FN(B200ATTN_FP16, true);
   else
-    fn = in_dtype == B200ATTN_BF16 ? (const void*)rope_kv_write_kernel<B200ATTN_BF16, false> : (const void*)rope_kv_write_kernel<B200ATTN_FP16, false>;
+    fn = in_dtype == B200ATTN_BF16 ? B200_ROPE_FN(B200ATTN_BF16, false) : B200_ROPE_FN(B200ATTN_FP16, false);
+#undef B200_ROPE_FN
   void* args[] = {&p};
   return launch_with_pdl(fn, dim3((unsigned)grid), dim3(block), 0, static_cast<cudaStream_t>(stream), args);
 }

@@ -68,6 +68,14 @@ for l in range(layers):
           f"pushed {q(rel(13) - rel(4)):4.2f}/{q(rel(13) - rel(4), np.max):4.2f}, received {q(rel(12) - rel(4)):4.2f}/{q(rel(12) - rel(4), np.max):4.2f}, exit {q(rel(5) - rel(4)):4.2f}/{q(rel(5) - rel(4), np.max):4.2f} | "
           f"exit min {x.min():7.2f} max {x.max():7.2f}{gap}")
     prev_exit = x.max()
+    if int(os.environ.get("B200_CLUSTER", "2")) == 2 and nc % 2 == 0 and len(a) == nc:
+        # what dynamic tile sharing inside a cluster could give: both halves of a pair would finish at the mean of their
+        # last-tile times instead of the later one
+        pa, pb = lt[0::2], lt[1::2]
+        cur, bal = np.maximum(pa, pb), (pa + pb) / 2
+        print(f"            pair view: later half - earlier half p50 {np.median(np.abs(pa - pb)):.2f} max {np.abs(pa - pb).max():.2f} us; "
+              f"slowest pair now {cur.max():.2f}, if balanced {bal.max():.2f} (p50 {np.median(cur):.2f} -> {np.median(bal):.2f}); "
+              f"lower half later in {int((pa > pb).sum())} of {len(pa)} pairs")
     if l == layers - 1 and int(os.environ.get("B200_CLUSTER", "2")) > 1:
         # per-SM view: do CTAs that have their SM to themselves finish earlier?
         smid = a[:, 6].astype(np.int64)
