@@ -14,17 +14,22 @@ namespace b200attn {
 // [0, Hv * tile_prefix[B]) enumerates (s, hv, tile) with tile fastest, then hv, then s.
 // CTA c owns x in [c * tpc, min((c + 1) * tpc, total)).
 // ------------------------------------------------------------------------------------------------
+constexpr int kPlanSmemSeqs = 4096;   // tile prefixes of up to this many rows are searched in shared memory
+
 __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ seq_lens, int B, int Hv, int grid,
                                                    const int32_t* __restrict__ block_table, int64_t bt_stride,
                                                    const int32_t* __restrict__ row_map, int cpb, int32_t* __restrict__ plan) {
   __shared__ int warp_sums[8];
   __shared__ int carry_s;
+  __shared__ int prefix_s[kPlanSmemSeqs + 1];
+  __shared__ int4 ent_s[kMaxGrid];          // (first chunk, seq_len, block-table row, live) of every CTA, for the id gather
   // No early griddepcontrol.launch_dependents here: kernels that follow may read the plan BEFORE their own
   // griddepcontrol.wait (decode prefetches K/V tiles early), so they must not start until this grid has completed.
   pdl_wait();
   int32_t* prefix = plan + kPlanPrefixOffset;
+  const bool in_smem = B <= kPlanSmemSeqs;   // the binary searches below then never touch global memory
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  for (int i = tid; i < kPlanCounterWords; i += 256) plan[kPlanCounterOffset + i] = 0;
+  for (int i = tid; i < kPlanCounterWords / 4; i += 256) reinterpret_cast<int4*>(plan + kPlanCounterOffset)[i] = make_int4(0, 0, 0, 0);
   if (tid == 0) carry_s = 0;
   __syncthreads();
   for (int base = 0; base < B; base += 256) {
@@ -45,13 +50,19 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
     int woff = 0;
     for (int k = 0; k < wid; ++k) woff += warp_sums[k];
     const int carry = carry_s;
-    if (i < B) prefix[i] = carry + woff + v - nt;  // exclusive
+    if (i < B) {
+      prefix[i] = carry + woff + v - nt;  // exclusive
+      if (in_smem) prefix_s[i] = carry + woff + v - nt;
+    }
     __syncthreads();
     if (tid == 255) carry_s = carry + woff + v;
     __syncthreads();
   }
   const int total_seq_tiles = carry_s;
-  if (tid == 0) prefix[B] = total_seq_tiles;
+  if (tid == 0) {
+    prefix[B] = total_seq_tiles;
+    if (in_smem) prefix_s[B] = total_seq_tiles;
+  }
   const long long total = (long long)total_seq_tiles * Hv;
   const int tpc = total > 0 ? (int)((total + grid - 1) / grid) : 1;
   if (tid == 0) {
@@ -63,7 +74,8 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
     plan[5] = cpb;
     plan[6] = plan[7] = 0;
   }
-  __syncthreads();  // prefix[] (global) written by this CTA is visible to it after the barrier
+  __syncthreads();  // prefix[] (global / shared) written by this CTA is visible to it after the barrier
+  const int* pf = in_smem ? prefix_s : prefix;
   int32_t* ent = plan + kPlanHeaderWords;
   for (int c = tid; c < grid; c += 256) {
     const long long x = (long long)c * tpc;
@@ -75,11 +87,11 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
       int lo = 0, hi = B;  // invariant: Hv*prefix[lo] <= x < Hv*prefix[hi]
       while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
-        if ((long long)prefix[mid] * Hv <= x) lo = mid; else hi = mid;
+        if ((long long)pf[mid] * Hv <= x) lo = mid; else hi = mid;
       }
       const int s = lo;
-      pfx = prefix[s];
-      const int nt = prefix[s + 1] - pfx;
+      pfx = pf[s];
+      const int nt = pf[s + 1] - pfx;
       const long long r = x - (long long)pfx * Hv;
       e.x = s;
       e.y = (int)(r / nt);
@@ -93,19 +105,20 @@ __global__ void __launch_bounds__(256) plan_kernel(const int32_t* __restrict__ s
     *reinterpret_cast<int4*>(d) = e;
     *reinterpret_cast<int4*>(d + 4) = make_int4(L, row, pfx, tpc);
     *reinterpret_cast<int4*>(d + 8) = make_int4(grid, B, 0, 0);
+    ent_s[c] = make_int4(e.z * (kTileTokens / kChunkTokens), L, row, e.x >= 0 ? 1 : 0);
   }
   __syncthreads();
   // block ids of the first 32 16-token chunks of every CTA's first segment: the decode producer issues its first TMA
-  // loads after ONE dependent load (this entry) instead of plan -> seq_lens -> row_map -> block_table
-  for (int idx = tid; idx < grid * kPlanEntryIds; idx += 256) {
-    const int c = idx / kPlanEntryIds, j = idx % kPlanEntryIds;
-    const int32_t* d = ent + (size_t)c * kPlanEntryWords;
+  // loads after ONE dependent load (this entry) instead of plan -> seq_lens -> row_map -> block_table.  One warp per CTA
+  // entry and pass: 32 independent block-table loads, one coalesced 128-byte store.
+  for (int c = wid; c < grid; c += 8) {
+    const int4 e = ent_s[c];
     int id = 0;
-    if (d[0] >= 0) {
-      const int ci = d[2] * (kTileTokens / kChunkTokens) + j;
-      if (ci * kChunkTokens < d[4]) id = block_table[(int64_t)d[5] * bt_stride + ci / cpb];
+    if (e.w) {
+      const int ci = e.x + lane;
+      if (ci * kChunkTokens < e.y) id = block_table[(int64_t)e.z * bt_stride + ci / cpb];
     }
-    ent[(size_t)c * kPlanEntryWords + kPlanEntryIds + j] = id;
+    ent[(size_t)c * kPlanEntryWords + kPlanEntryIds + lane] = id;
   }
 }
 
