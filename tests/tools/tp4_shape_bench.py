@@ -24,7 +24,11 @@ out = torch.zeros(NL, B, Hq, D, dtype=torch.bfloat16, device=dev)
 ks = torch.full((Hkv,), 0.01, device=dev); vs = torch.full((Hkv,), 0.01, device=dev)
 nbytes = 2 * B * L * Hkv * D + 4 * B * Hq * D + B * nblk * 4
 ref = None
-for ctas, cluster, fused in [(None, 2, True), (None, 2, False), (256, 2, True), (256, 2, False), (256, 8, True), (256, 4, True), (128, 4, True), (288, 2, True), (296, 2, True)]:
+VARIANTS = [(None, 2, True), (None, 2, False), (256, 2, True), (256, 2, False), (256, 8, True), (256, 4, True), (128, 4, True), (288, 2, True), (296, 2, True)]
+if os.environ.get("B200_OVERSUB"):   # more CTAs than resident slots: the block scheduler balances the waves
+    VARIANTS = [(None, 2, True), (256, 2, True), (384, 2, True), (384, 1, True), (512, 2, True), (512, 1, True), (512, 4, True), (768, 2, True), (768, 1, True), (1024, 2, True),
+                (512, 2, False), (1024, 2, False)]
+for ctas, cluster, fused in VARIANTS:
     lib.b200attn_set_option(b"cluster", cluster)
     ws = ops.DecodeWorkspace(dev, B, torch.uint8, num_ctas=ctas, group_size=Hq // Hkv)
     ws.make_plan(lens, Hq, Hkv, bt, bs)
