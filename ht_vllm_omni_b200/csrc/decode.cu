@@ -158,7 +158,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
       const int L = sg == 0 ? cx.x : max(__ldg(p.seq_lens + s), 0);
       const int nt = (L + kTileTokens - 1) / kTileTokens;
       const int n = min(remaining, nt - tile);
-      const int kvh = hv / p.gsplit;
+      const int kvh = (int)p.d_gsplit.div((uint32_t)hv);
       const int row = sg == 0 ? cx.y : (p.row_map ? __ldg(p.row_map + s) : s);
       const int32_t* bt = p.block_table + (int64_t)row * p.bt_stride;
       const int pfx = sg == 0 ? cx.z : __ldg(p.plan + kPlanPrefixOffset + s);
@@ -192,7 +192,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
         const int tl = tile + tt;
         if ((tt & 7) == 0) {  // refill 32 block ids (8 tiles) with one coalesced load
           const int ci = (tl << 2) + lane;
-          blk = (sg == 0 && tt == 0) ? first_ids : ((ci * kChunkTokens < L) ? __ldg(bt + ci / p.cpb) : 0);
+          blk = (sg == 0 && tt == 0) ? first_ids : ((ci * kChunkTokens < L) ? __ldg(bt + p.d_cpb.div((uint32_t)ci)) : 0);
         }
         mbar_wait(empty_bar(stage), phase ^ 1);
         const int tok0 = tl * kTileTokens;
@@ -206,14 +206,14 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
           // the chunk's 16 K scales and 16 V scales: 64 contiguous bytes each in the [block][head][slot] side caches
           if (lane >= 8 && lane < 16 && c < nvalid) {
             const int ci = (tl << 2) + c;
-            const int row0 = (ci % p.cpb) * kChunkTokens;
+            const int row0 = (int)((uint32_t)ci - p.d_cpb.div((uint32_t)ci) * (uint32_t)p.cpb) * kChunkTokens;
             const float* src = (kv ? p.vs_cache : p.ks_cache) + (int64_t)b * p.sc_stride_block + (int64_t)kvh * p.sc_stride_head + row0;
             bulk_load_1d(dyn_base + stage * kDynStageBytes + kv * (kTileTokens * 4) + c * (kChunkTokens * 4), src, kChunkTokens * 4, full_bar(stage));
           }
         }
         if (lane < 8 && c < nvalid) {
           const int ci = (tl << 2) + c;
-          const int row0 = (ci % p.cpb) * kChunkTokens;
+          const int row0 = (int)((uint32_t)ci - p.d_cpb.div((uint32_t)ci) * (uint32_t)p.cpb) * kChunkTokens;
           const uint32_t dst = stages_base + stage * kStageBytes + (kv ? kConsumerWarps * kChunkBytes : 0) + c * kChunkBytes;
           const CUtensorMap* tm = kv ? &tm_v : &tm_k;
           if constexpr (kFp8) {
@@ -269,7 +269,7 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
     const int n = desc[slot * 8 + 3];
     const int L = desc[slot * 8 + 4];
     const int pfx = desc[slot * 8 + 5];
-    const int kvh = hv / p.gsplit;
+    const int kvh = (int)p.d_gsplit.div((uint32_t)hv);
 
     // ---- Q fragments (B operand: n = head g (+8), k = permuted head-dim) ----
     uint32_t qb[NT][8][2];
@@ -754,6 +754,7 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.B = num_seqs; p.Hq = num_q_heads; p.Hv = num_kv_heads * gsplit; p.G = G; p.gsplit = gsplit;
   p.cpb = block_size / kChunkTokens;
+  p.d_cpb.init((uint32_t)p.cpb); p.d_gsplit.init((uint32_t)gsplit);
   p.cluster = 1;
   p.debug = option_debug();
   p.dbg = option_debug_buffer();

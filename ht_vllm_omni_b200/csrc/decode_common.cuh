@@ -26,6 +26,8 @@ struct DecodeParams {
   int G;                // query heads per virtual kv head (<= 16)
   int gsplit;           // virtual heads per physical kv head
   int cpb;              // 16-token chunks per cache block (block_size / 16)
+  FastDiv d_cpb, d_gsplit;   // multiply-shift forms of the two launch-constant divisors (the producer's first-TMA path ran three
+                             // integer-divide sequences otherwise)
   int fresh;            // trailing positions of a row the preceding kernel may have written (< 0: unknown, no early prefetch)
   int fused_merge;      // 1: the last CTA to finish a split (sequence, kv head) pair merges its partials in-kernel
   int cluster;          // thread-block cluster size of this launch (1: none); partials of a pair whose CTAs share a cluster

@@ -252,7 +252,9 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
     named_bar_sync(kSetupBar, kSetupThreads);
     tc_fence_after();
   }
-  if (p.cluster > 1) cluster_arrive_release();   // "my barriers are initialised"; waited for only by CTAs that push to a peer
+  // "my barriers are initialised"; waited for only by CTAs that push to a peer.  The producer warp arrives AFTER it has issued
+  // its first tile's TMA loads: a cluster-scope release is a fence, and nothing the peer waits for is produced by this warp.
+  if (p.cluster > 1 && warp != 4) cluster_arrive_release();
   pdl_launch_dependents();
   if (chk.x != (int)gridDim.x || chk.y != p.B) __trap();   // plan / launch mismatch
   const int L_first = cx.x;
@@ -260,6 +262,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
 
   if (warp == 4) {
     // =========================================== producer ===========================================
+    bool cl_arrived = false;
     if (!idle) {
     const uint64_t pol = policy_evict_first();
     TcCursor cur; cur.init(cs, L_first);
@@ -280,19 +283,19 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       if (cur.first()) {
         const int row = cur.sg == 0 ? row_first : (p.row_map ? __ldg(p.row_map + cur.seg_s) : cur.seg_s);
         bt = p.block_table + (int64_t)row * p.bt_stride;
-        kvh = cur.seg_hv / p.gsplit;
+        kvh = (int)p.d_gsplit.div((uint32_t)cur.seg_hv);
         if (cur.sg == 0) {
           blk = e1;   // the plan entry carries the first 32 block ids: no dependent load before the first TMA
         } else {
           const int ci = (tok0 >> 4) + lane;
-          blk = (ci * kChunkTokens < cur.seg_L) ? __ldg(bt + ci / p.cpb) : 0;
+          blk = (ci * kChunkTokens < cur.seg_L) ? __ldg(bt + p.d_cpb.div((uint32_t)ci)) : 0;
         }
       } else if ((cur.u & 3) == 0) {
         blk = blk_next;
       }
       if ((cur.u & 3) == 1 && (cur.u | 3) + 1 < cur.m) {  // ids of MMA tiles [4k+4, 4k+8): requested three tiles ahead of their use
         const int ci = (tok0 >> 4) + 24 + lane;
-        blk_next = (ci * kChunkTokens < cur.seg_L) ? __ldg(bt + ci / p.cpb) : 0;
+        blk_next = (ci * kChunkTokens < cur.seg_L) ? __ldg(bt + p.d_cpb.div((uint32_t)ci)) : 0;
       }
       // K/V tiles that lie entirely below L - fresh cannot have been touched by the kernel before us: they are requested
       // BEFORE griddepcontrol.wait (programmatic dependent launch), at most one ring fill
@@ -346,7 +349,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       const int c = lane & 7;
       const int b = __shfl_sync(0xffffffffu, blk, ((cur.u & 3) << 3) + c);
       const int ci = (tok0 >> 4) + c;
-      const int row0 = (ci % p.cpb) * kChunkTokens;
+      const int row0 = (int)((uint32_t)ci - p.d_cpb.div((uint32_t)ci) * (uint32_t)p.cpb) * kChunkTokens;
       mbar_wait(kempty(st), par);
       if (kDbg && it == 0 && lane == 0) dbg_stamp(p, 14);
       if (lane == 0) mbar_arrive_expect_tx(kfull(st), (uint32_t)nbox * kTcBoxBytes);
@@ -358,10 +361,12 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       __syncwarp();
       if (lane >= 8 && lane < 16 && c < nbox) tma_load_4d(v_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_v, vfull(st), 0, row0, kvh, b, pol);
       if (kDbg && it == 0 && lane == 0) dbg_stamp(p, 2);
+      if (it == 0 && p.cluster > 1) { cluster_arrive_release(); cl_arrived = true; }
       ++it;
     }
     if (!waited) pdl_wait();
     }
+    if (p.cluster > 1 && !cl_arrived) cluster_arrive_release();   // idle CTA / empty range: still owed to the cluster barrier
   } else {
     const uint32_t tmem = *tmem_ptr_smem;
     if (kDbg && threadIdx.x == 0) dbg_stamp(p, 1);
@@ -489,7 +494,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       };
       auto prep_q = [&]() {
         const uint32_t slot = qc.sg & 1;
-        const int kvh = qc.seg_hv / p.gsplit;
+        const int kvh = (int)p.d_gsplit.div((uint32_t)qc.seg_hv);
         const int h = qh, part = qpart;
         float kscale = 0.f;
         if (part == 0) kscale = __ldg(p.k_scale + (int64_t)kvh * p.scale_stride);   // in flight while the query arrives
@@ -540,7 +545,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
           // how this segment ends is known now: decide it here, off the tail's critical path
           //   0 whole sequence -> final output     1 partial to the workspace (merge kernel follows)
           //   2 in-kernel merge through L2 (ticket / publish)     3 fold along the cluster chain (distributed shared memory)
-          seg_vscale = __ldg(p.v_scale + (int64_t)(cur.seg_hv / p.gsplit) * p.scale_stride);
+          seg_vscale = __ldg(p.v_scale + (int64_t)((int)p.d_gsplit.div((uint32_t)cur.seg_hv)) * p.scale_stride);
           const bool whole_seg = (cur.seg_tile0 == 0) && ((cur.seg_tile0 + cur.seg_n) * kTileTokens >= cur.seg_L);
           seg_mode = 0;
           if (!whole_seg) {
@@ -674,7 +679,7 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
           named_bar_sync(1, 128);
           if (kDbg && tid == 0 && cur.remaining <= 0) dbg_stamp(p, 11);
           const int s = cur.seg_s, hv = cur.seg_hv, L = cur.seg_L;
-          const int kvh = hv / p.gsplit;
+          const int kvh = (int)p.d_gsplit.div((uint32_t)hv);
           const float vscale = seg_vscale;
           const int pslot = cur.sg == 0 ? 0 : 1;
           const int d = tid;
