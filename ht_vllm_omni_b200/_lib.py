@@ -95,6 +95,11 @@ def load_library():
             fn.argtypes = args
         if lib.b200attn_abi_version() != ABI_VERSION:
             raise B200AttnError("libb200attn ABI version mismatch")
+        # runtime knobs from the environment: B200ATTN_OPT_<name>=<int> -> b200attn_set_option (see include/b200attn.h)
+        for k, v in os.environ.items():
+            if k.startswith("B200ATTN_OPT_"):
+                if lib.b200attn_set_option(k[len("B200ATTN_OPT_"):].lower().encode(), int(v)) < 0 and int(v) >= 0:
+                    pass   # unknown names are reported by b200attn_last_error(); previous value 0 also returns 0
         _LIB = lib
         return lib
 
