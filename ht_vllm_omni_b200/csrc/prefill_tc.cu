@@ -28,6 +28,9 @@
 
 namespace b200attn {
 
+#ifndef B200_PF_HALF2
+#define B200_PF_HALF2 1   // probabilities in f16x2 from the exponent on (0: the fp32 / integer-rounding path of the first version)
+#endif
 constexpr int kPfThreads = 320;
 constexpr int kPfSoftmaxThreads = 256;
 constexpr int kPfProducerWarp = 8, kPfMmaWarp = 9;
@@ -437,6 +440,39 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 #pragma unroll
         for (int c = 0; c < 4; ++c) {               // 16 tokens -> one 16-byte chunk of each operand row
           uint32_t h4[4], l4[4];
+#if B200_PF_HALF2
+          // two elements per instruction from the exponent on: t = x crow + off in fp32, packed to f16x2 (|t| < 16 wherever p'
+          // matters: spacing <= 2^-7, i.e. p' good to 0.3 %, the precision the 8-bit hi + lo operand keeps anyway), ex2.f16x2,
+          // hi = e4m3(p'), lo = e4m3(p' - hi), and the row sum carried as f16x2 partial sums of 16 values (exact to 2^-11 each)
+          uint32_t sacc = 0u;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            uint32_t hb[2], lb[2], pp[2];
+#pragma unroll
+            for (int q2 = 0; q2 < 2; ++q2) {
+              const float t0 = fmaf(__uint_as_float(sr[c * 16 + w * 4 + 2 * q2]), crow, off);
+              const float t1 = fmaf(__uint_as_float(sr[c * 16 + w * 4 + 2 * q2 + 1]), crow, off);
+              uint32_t t2, p2, back, d2;
+              uint16_t hi2, lo2;
+              asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(t2) : "f"(t1), "f"(t0));
+              asm("ex2.approx.f16x2 %0, %1;" : "=r"(p2) : "r"(t2));
+              asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(hi2) : "r"(p2));
+              asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(back) : "h"(hi2));
+              asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(d2) : "r"(p2), "r"(back));
+              asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(lo2) : "r"(d2));
+              hb[q2] = hi2; lb[q2] = lo2; pp[q2] = p2;
+            }
+            h4[w] = hb[0] | (hb[1] << 16);
+            l4[w] = lb[0] | (lb[1] << 16);
+            uint32_t s2;
+            asm("add.rn.f16x2 %0, %1, %2;" : "=r"(s2) : "r"(pp[0]), "r"(pp[1]));
+            asm("add.rn.f16x2 %0, %1, %2;" : "=r"(sacc) : "r"(sacc), "r"(s2));
+          }
+          {
+            const float2 sf = __half22float2(*reinterpret_cast<const __half2*>(&sacc));
+            l_run += sf.x + sf.y;
+          }
+#else
 #pragma unroll
           for (int w = 0; w < 4; ++w) {
             float pv[4];
@@ -447,6 +483,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             }
             pf_split4_pos(pv, h4[w], l4[w]);
           }
+#endif
           const uint32_t a = p_base + (2 * b) * kPfTileBytes + pf_swz(row, half * 4 + c);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(h4[0]), "r"(h4[1]), "r"(h4[2]), "r"(h4[3]) : "memory");
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a + kPfTileBytes), "r"(l4[0]), "r"(l4[1]), "r"(l4[2]), "r"(l4[3]) : "memory");
