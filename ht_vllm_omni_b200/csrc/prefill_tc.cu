@@ -28,6 +28,9 @@
 
 namespace b200attn {
 
+#ifndef B200_PF_PTMEM
+#define B200_PF_PTMEM 1   // P (hi, lo) as the TMEM-resident A operand of the second GEMM (0: staged in shared memory)
+#endif
 #ifndef B200_PF_HALF2
 #define B200_PF_HALF2 1   // probabilities in f16x2 from the exponent on (0: the fp32 / integer-rounding path of the first version)
 #endif
@@ -83,6 +86,21 @@ __device__ __forceinline__ void pf_mma_f8(uint32_t d_tmem, uint64_t a_desc, uint
       "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// A operand read from TENSOR MEMORY (row = TMEM lane, 4 e4m3 elements per 32-bit column, K ascending with the column)
+__device__ __forceinline__ void pf_mma_f8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void pf_st16_nowait(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
 }
 __device__ __forceinline__ void pf_commit(uint32_t bar) {
@@ -293,8 +311,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           for (int k = 0; k < nk; ++k) {
             if (kDbg && p.variant == 2) break;
             const uint64_t db = pf_desc(v_base + st * kPfTileBytes + k * 4096, 0, 1024);
+#if B200_PF_PTMEM
+            // P lives in TMEM columns [384, 512): buffer b = 64 columns (32 hi + 32 lo), a 32-token K step = 8 columns
+            pf_mma_f8_ts(tmem + 256, tmem + 384 + b * 64 + k * 8, db, kPfIdescPV, (j > 0 || k > 0) ? 1u : 0u);
+            if (!kDbg || p.variant != 3) pf_mma_f8_ts(tmem + 256, tmem + 384 + b * 64 + 32 + k * 8, db, kPfIdescPV, 1u);
+#else
             pf_mma_f8(tmem + 256, pf_desc(p_base + (2 * b) * kPfTileBytes + k * 32, 16, 1024), db, kPfIdescPV, (j > 0 || k > 0) ? 1u : 0u);
             if (!kDbg || p.variant != 3) pf_mma_f8(tmem + 256, pf_desc(p_base + (2 * b + 1) * kPfTileBytes + k * 32, 16, 1024), db, kPfIdescPV, 1u);
+#endif
           }
           pf_commit(vempty(st));
           pf_commit(pempty(b));
@@ -437,6 +461,9 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         // ---- p' = 2^(x - m + 4), row sum, hi / lo split, A-operand rows of the second GEMM ----
         wait_t(pempty(b), ((j >> 1) & 1) ^ 1, 1);   // PV of tile j-2 no longer reads this P buffer
         const float off = kPfShift - m_run;
+#if B200_PF_PTMEM
+        uint32_t hw[16], lw[16];                    // this thread's 64 tokens of the row: hi bytes, lo bytes
+#endif
 #pragma unroll
         for (int c = 0; c < 4; ++c) {               // 16 tokens -> one 16-byte chunk of each operand row
           uint32_t h4[4], l4[4];
@@ -484,10 +511,22 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             pf_split4_pos(pv, h4[w], l4[w]);
           }
 #endif
+#if B200_PF_PTMEM
+#pragma unroll
+          for (int w = 0; w < 4; ++w) { hw[c * 4 + w] = h4[w]; lw[c * 4 + w] = l4[w]; }
+#else
           const uint32_t a = p_base + (2 * b) * kPfTileBytes + pf_swz(row, half * 4 + c);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(h4[0]), "r"(h4[1]), "r"(h4[2]), "r"(h4[3]) : "memory");
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a + kPfTileBytes), "r"(l4[0]), "r"(l4[1]), "r"(l4[2]), "r"(l4[3]) : "memory");
+#endif
         }
+#if B200_PF_PTMEM
+        // the A operand of the second GEMM goes to tensor memory: no shared-memory write here and no shared-memory read by the MMA
+        pf_st16_nowait(tmem + lane_base + 384 + b * 64 + half * 16, hw);
+        pf_st16_nowait(tmem + lane_base + 384 + b * 64 + 32 + half * 16, lw);
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        pf_fence_before();
+#endif
         {
           // rows of the V tile past the valid count that the last 32-token MMA step still reads: stale smem or cache slots
           // beyond seq_len (possibly NaN patterns) must not meet p = 0
