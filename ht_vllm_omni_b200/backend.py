@@ -199,10 +199,13 @@ class B200PagedAttentionMetadataBuilder(AttentionMetadataBuilder[B200PagedAttent
         """Two-op contract: every launch reads the builder's fixed buffers, so one FULL graph serves any batch (ALWAYS).
         When forward() owns the KV write, a pure-decode step takes the in-kernel-write launch, which is only valid for one
         token per request -- a host-side choice that a captured graph would freeze.  FULL graphs are therefore offered for
-        uniform single-token decode batches only (what FlashInfer's TRT-LLM decode path declares too,
-        $VLLM/v1/attention/backends/flashinfer.py); mixed batches run the hooks eagerly between piecewise graphs."""
+        UNIFORM batches only (every request the same query length: plain decode, or 1 + k spec-decode tokens); mixed batches
+        run the hooks eagerly between piecewise graphs."""
         if B200PagedAttentionBackend.forward_includes_kv_cache_update:
-            return AttentionCGSupport.UNIFORM_SINGLE_TOKEN_DECODE
+            # uniform batches: q_len == 1 decodes take the in-kernel-write launch, q_len == 1 + k (spec-decode / the talker's
+            # MTP verification, vllm_omni/worker/gpu_model_runner.py:1266-1303) the general one; a graph captured for one
+            # uniform query length is only ever replayed for that length, so the host-side choice is graph-key invariant
+            return AttentionCGSupport.UNIFORM_BATCH
         return cls._cudagraph_support
 
     def __init__(self, kv_cache_spec, layer_names, vllm_config, device):

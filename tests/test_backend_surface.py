@@ -20,7 +20,7 @@ def test_backend_static_surface():
     assert be.get_impl_cls() is B.B200PagedAttentionImpl and be.get_builder_cls() is B.B200PagedAttentionMetadataBuilder
     assert be.forward_includes_kv_cache_update is True and be.accept_output_buffer is True   # B200ATTN_SEPARATE_KV_UPDATE unset
     bc = be.get_builder_cls()
-    assert bc.get_cudagraph_support(None, None) == vllm_backend.AttentionCGSupport.UNIFORM_SINGLE_TOKEN_DECODE
+    assert bc.get_cudagraph_support(None, None) == vllm_backend.AttentionCGSupport.UNIFORM_BATCH
     assert be.get_kv_cache_shape(10, 16, 4, 128, "fp8") == (10, 2, 16, 4, 128)
     assert be.get_kv_cache_block_dim(16, 4, 128) == 0
     assert be.get_kv_cache_stride_order() == (0, 1, 3, 2, 4)

@@ -234,3 +234,82 @@ def test_full_graph_captures_forward_only_and_build_runs_eagerly_before_each_rep
         got = out.view(T, Hq, D).float().cpu().numpy()
         err = np.abs(got - ref)
         assert np.all(err <= 1e-2 + np.maximum(np.abs(ref), 2.0 ** -14) * 2.0 ** -7), float(err.max())
+
+
+def test_uniform_spec_decode_batch_under_full_graph_with_the_forward_writes_contract():
+    """AttentionCGSupport.UNIFORM_BATCH under the default contract: a FULL graph captured for a uniform batch of q_len = 1 + k
+    (spec-decode verification / the talker's MTP step) holds forward() only -- KV write of the 1 + k tokens, the rows, the
+    prefill kernel -- and is replayed for other sequence lengths and for a padded batch (fewer live requests); build() runs
+    eagerly before every replay, as in vLLM."""
+    from ht_vllm_omni_b200 import backend as B
+
+    be = B.B200PagedAttentionBackend
+    assert be.forward_includes_kv_cache_update
+    assert be.get_builder_cls().get_cudagraph_support(None, None) == vb.AttentionCGSupport.UNIFORM_BATCH
+    Hq, Hkv, D, bs, R, QL = 16, 2, 128, 16, 4, 3
+    T = R * QL
+    impl = be.get_impl_cls()(Hq, D, D ** -0.5, Hkv, None, None, "fp8")
+    ks, vs = torch.tensor([0.02], device="cuda"), torch.tensor([0.03], device="cuda")
+    layer = types.SimpleNamespace(_k_scale=ks, _v_scale=vs)
+    max_lens = np.array([700, 300, 1500, 64], np.int32)
+    bt_np, nb = O.make_block_table(max_lens, bs, seed=4)
+    kv_cache = _alloc_like_vllm(be, nb, bs, Hkv, D, "fp8", torch.uint8)
+    rng = np.random.default_rng(1)
+    base_k = rng.integers(0, 0x78, (nb, bs, Hkv, D), dtype=np.uint8); base_v = rng.integers(0, 0x78, (nb, bs, Hkv, D), dtype=np.uint8)
+    d_seq = torch.zeros(R, dtype=torch.int32, device="cuda"); d_bt = torch.from_numpy(bt_np).cuda()
+    d_qsl = torch.zeros(R + 1, dtype=torch.int32, device="cuda")
+    d_slots = torch.full((T,), -1, dtype=torch.int64, device="cuda")
+    g = torch.Generator().manual_seed(2)
+    q = torch.randn(T, Hq * D, generator=g).to(torch.bfloat16).cuda()
+    kn = torch.randn(T, Hkv * D, generator=g).to(torch.bfloat16).cuda(); vn = torch.randn(T, Hkv * D, generator=g).to(torch.bfloat16).cuda()
+    out = torch.zeros(T, Hq * D, dtype=torch.bfloat16, device="cuda")
+    builder = be.get_builder_cls()(types.SimpleNamespace(block_size=bs, dtype=torch.uint8), ["l0"], _cfg(Hq, Hkv, D, 64), torch.device("cuda"))
+
+    def metadata(seq, live):
+        """`live` requests of QL tokens each, the rest of the captured batch is padding (seq_len 0, repeated offsets, slot -1)"""
+        qsl = np.minimum(np.arange(R + 1), live) * QL
+        sl = np.zeros(R, np.int32); sl[:live] = seq[:live]
+        d_seq.copy_(torch.from_numpy(sl)); d_qsl.copy_(torch.from_numpy(qsl.astype(np.int32)))
+        pos = [(r, p) for r in range(live) for p in range(int(seq[r]) - QL, int(seq[r]))]
+        slots = np.full(T, -1, np.int64); slots[:live * QL] = O.slots_for_positions(bt_np, pos, bs)
+        d_slots.copy_(torch.from_numpy(slots))
+        return vb.CommonAttentionMetadata(query_start_loc=d_qsl, query_start_loc_cpu=torch.from_numpy(qsl.astype(np.int32)), seq_lens=d_seq,
+                                          num_reqs=R, num_actual_tokens=T, max_query_len=QL, max_seq_len=2048, block_table_tensor=d_bt,
+                                          slot_mapping=d_slots), slots
+
+    def reference(seq, live, slots):
+        kc, vc = base_k.copy(), base_v.copy()
+        O.kv_write_ref(kn.view(T, Hkv, D).float().cpu().numpy(), vn.view(T, Hkv, D).float().cpu().numpy(), kc, vc, slots, np.array([0.02], np.float32),
+                       np.array([0.03], np.float32), fp8=True)
+        rows = live * QL
+        row_req = np.repeat(np.arange(live), QL)
+        row_len = np.concatenate([seq[r] - QL + 1 + np.arange(QL) for r in range(live)]).astype(np.int32)
+        return O.paged_decode_exact(q.view(T, Hq, D).float().cpu().numpy()[:rows], kc, vc, bt_np[row_req], row_len, D ** -0.5,
+                                    np.array([0.02], np.float32), np.array([0.03], np.float32), fp8=True), rows
+
+    first = (np.array([700, 300, 1500, 64]), 4)
+    cm, _ = metadata(*first)
+    md = builder.build_for_cudagraph_capture(cm)
+    assert not md.pure_decode
+
+    def hooks():
+        impl.forward(layer, q, kn, vn, kv_cache, md, out)
+
+    s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        hooks()
+    torch.cuda.current_stream().wait_stream(s); torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        hooks()
+    for seq, live in (first, (np.array([650, 280, 1400, 40]), 4), (np.array([123, 999, 0, 0]), 2)):
+        kv_cache[:, 0].copy_(torch.from_numpy(base_k)); kv_cache[:, 1].copy_(torch.from_numpy(base_v))
+        cm, slots = metadata(seq, live)
+        builder.build(0, cm)            # eager, outside the graph
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        ref, rows = reference(seq, live, slots)
+        got = out.view(T, Hq, D).float().cpu().numpy()[:rows]
+        err = np.abs(got - ref)
+        assert np.all(err <= 1e-2 + np.maximum(np.abs(ref), 2.0 ** -14) * 2.0 ** -7), (live, float(err.max()))
