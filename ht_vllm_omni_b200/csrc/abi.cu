@@ -15,6 +15,7 @@ static int g_opt_pdl = 1;
 static int g_opt_force_simt = 0;
 static int g_opt_debug = 0;
 static int g_opt_tc = 1;
+static int g_opt_big_box = 1;       // tcgen05 decode: one TMA box per min(block_size, 64) tokens instead of one per 16
 static int g_opt_fused_write = 1;   // b200attn_decode_kv_write writes the new token inside the decode kernel when it can
 static int g_opt_cluster = 2;   // thread-block cluster size of the tcgen05 decode kernel (1 = no clusters)
 static unsigned long long* g_dbg_buf = nullptr;
@@ -38,6 +39,7 @@ int option_debug() { return g_opt_debug; }
 int option_tc() { return g_opt_tc; }
 int option_cluster() { return g_opt_cluster; }
 int option_fused_write() { return g_opt_fused_write; }
+int option_big_box() { return g_opt_big_box; }
 unsigned long long* option_debug_buffer() { return g_dbg_buf; }
 
 int launch_with_pdl_cluster(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args, int cluster) {
@@ -88,7 +90,7 @@ static void resolve_encode() {
 // K or V plane of the paged cache as a 4-D tensor (D, block_size, Hkv, num_blocks), box = 16 tokens x 128 bytes,
 // 128-byte swizzle so that both the row-wise K reads and the column-gathering V reads are bank-conflict free.
 int encode_kv_tensor_map(CUtensorMap* tm, const void* base, int kv_dtype, int64_t stride_block, int64_t stride_slot,
-                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D) {
+                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D, int box_tokens) {
   std::call_once(g_encode_once, resolve_encode);
   if (!g_encode) {
     if (g_encode_err != cudaSuccess) return check_cuda(g_encode_err, "cudaGetDriverEntryPoint(cuTensorMapEncodeTiled)");
@@ -107,7 +109,7 @@ int encode_kv_tensor_map(CUtensorMap* tm, const void* base, int kv_dtype, int64_
   }
   cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)block_size, (cuuint64_t)Hkv, (cuuint64_t)num_blocks};
   cuuint64_t strides[3] = {(cuuint64_t)(stride_slot * es), (cuuint64_t)(stride_head * es), (cuuint64_t)(stride_block * es)};
-  cuuint32_t box[4] = {(cuuint32_t)(fp8 ? 128 : 64), (cuuint32_t)kChunkTokens, 1, 1};
+  cuuint32_t box[4] = {(cuuint32_t)(fp8 ? 128 : 64), (cuuint32_t)box_tokens, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   const CUtensorMapDataType dt = fp8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16;
   CUresult r = g_encode(tm, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -157,6 +159,7 @@ extern "C" int b200attn_set_option(const char* name, int32_t value) {
   else if (!strcmp(name, "tc")) slot = &g_opt_tc;
   else if (!strcmp(name, "cluster")) slot = &g_opt_cluster;
   else if (!strcmp(name, "fused_write")) slot = &g_opt_fused_write;
+  else if (!strcmp(name, "big_box")) slot = &g_opt_big_box;
   if (!slot) {
     set_error("set_option: unknown option '%s'", name);
     return B200ATTN_EINVAL;

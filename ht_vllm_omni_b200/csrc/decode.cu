@@ -586,12 +586,13 @@ decode_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ 
 // host side
 // ------------------------------------------------------------------------------------------------
 int encode_kv_tensor_map(CUtensorMap* tm, const void* base, int kv_dtype, int64_t stride_block, int64_t stride_slot,
-                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D);
+                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D, int box_tokens = kChunkTokens);
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
 int option_force_simt();
 int option_debug();
 int option_tc();
 int option_fused_write();
+int option_big_box();
 int launch_decode_tc(const CUtensorMap& tk, const CUtensorMap& tv, DecodeParams& p, int grid, int q_dtype, cudaStream_t stream);
 int launch_decode_simt(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t out_stride_t, int64_t out_stride_h,
                        const void* k_cache, const void* v_cache, int64_t stride_block, int64_t stride_slot, int64_t stride_head,
@@ -732,10 +733,18 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
     return B200ATTN_EINVAL;
   }
 
+  // The tcgen05 kernel takes one TMA box per min(block_size, 64) tokens (block_size 32 / >= 64: half / a quarter of the
+  // UTMALDG instructions per byte; the swizzled smem image is the same as that of consecutive 16-token boxes).  64 is the
+  // limit because a piece of a row may start on any 64-token plan tile, so a 128-token box could straddle two cache blocks.
+  const bool use_tc = dyn == nullptr && fp8 && G <= 8 && option_tc();
+  const int cpb = block_size / kChunkTokens;
+  const int box_chunks = (use_tc && option_big_box() && (cpb & (cpb - 1)) == 0) ? (cpb < 4 ? cpb : 4) : 1;
   CUtensorMap tk, tv;
-  int rc = encode_kv_tensor_map(&tk, k_cache, kv_dtype, stride_block, stride_slot, stride_head, num_blocks, block_size, num_kv_heads, kD);
+  int rc = encode_kv_tensor_map(&tk, k_cache, kv_dtype, stride_block, stride_slot, stride_head, num_blocks, block_size, num_kv_heads, kD,
+                                box_chunks * kChunkTokens);
   if (rc) return rc;
-  rc = encode_kv_tensor_map(&tv, v_cache, kv_dtype, stride_block, stride_slot, stride_head, num_blocks, block_size, num_kv_heads, kD);
+  rc = encode_kv_tensor_map(&tv, v_cache, kv_dtype, stride_block, stride_slot, stride_head, num_blocks, block_size, num_kv_heads, kD,
+                            box_chunks * kChunkTokens);
   if (rc) return rc;
 
   DecodeParams p;
@@ -753,7 +762,7 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
   p.lse_out = lse_out;
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.B = num_seqs; p.Hq = num_q_heads; p.Hv = num_kv_heads * gsplit; p.G = G; p.gsplit = gsplit;
-  p.cpb = block_size / kChunkTokens;
+  p.cpb = cpb; p.box_chunks = box_chunks;
   p.d_cpb.init((uint32_t)p.cpb); p.d_gsplit.init((uint32_t)gsplit);
   p.cluster = 1;
   p.debug = option_debug();
@@ -788,7 +797,6 @@ static int decode_impl(const void* q, int64_t q_stride_t, int64_t q_stride_h, vo
     return q_dtype == B200ATTN_BF16 ? launch_decode<B200ATTN_FP8_E4M3, B200ATTN_BF16, 1, true>(tk, tv, p, num_ctas, st)
                                     : launch_decode<B200ATTN_FP8_E4M3, B200ATTN_FP16, 1, true>(tk, tv, p, num_ctas, st);
   }
-  const bool use_tc = fp8 && G <= 8 && option_tc();
   if (nw != nullptr) {
     // In-kernel write: the tcgen05 kernel, rows == tokens (no row_map: with several query tokens per request a later row
     // reads what an earlier row's CTA writes).  Every other shape runs the KV-write kernel first -- same result, two launches.

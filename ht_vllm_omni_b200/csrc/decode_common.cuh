@@ -26,6 +26,7 @@ struct DecodeParams {
   int G;                // query heads per virtual kv head (<= 16)
   int gsplit;           // virtual heads per physical kv head
   int cpb;              // 16-token chunks per cache block (block_size / 16)
+  int box_chunks;       // 16-token chunks one TMA box covers (tcgen05 kernel: min(cpb, 4) when a power of two, else 1)
   FastDiv d_cpb, d_gsplit;   // multiply-shift forms of the two launch-constant divisors (the producer's first-TMA path ran three
                              // integer-divide sequences otherwise)
   int fresh;            // trailing positions of a row the preceding kernel may have written (< 0: unknown, no early prefetch)

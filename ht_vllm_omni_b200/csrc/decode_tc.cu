@@ -344,9 +344,11 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
           nt_stored = true;
         }
       }
-      const int nbox = (cur.valid() + kChunkTokens - 1) / kChunkTokens;
+      const int per = p.box_chunks;   // 16-token chunks per TMA box: whole boxes are loaded (the cache block is allocated whole)
+      const int nbox = ((cur.valid() + kChunkTokens - 1) / kChunkTokens + per - 1) & ~(per - 1);
       const uint32_t st = it % kTcStages, par = ((it / kTcStages) & 1) ^ 1;
       const int c = lane & 7;
+      const bool issue = c < nbox && (c & (per - 1)) == 0;
       const int b = __shfl_sync(0xffffffffu, blk, ((cur.u & 3) << 3) + c);
       const int ci = (tok0 >> 4) + c;
       const int row0 = (int)((uint32_t)ci - p.d_cpb.div((uint32_t)ci) * (uint32_t)p.cpb) * kChunkTokens;
@@ -354,12 +356,12 @@ decode_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant
       if (kDbg && it == 0 && lane == 0) dbg_stamp(p, 14);
       if (lane == 0) mbar_arrive_expect_tx(kfull(st), (uint32_t)nbox * kTcBoxBytes);
       __syncwarp();
-      if (lane < 8 && c < nbox) tma_load_4d(k_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_k, kfull(st), 0, row0, kvh, b, pol);
+      if (lane < 8 && issue) tma_load_4d(k_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_k, kfull(st), 0, row0, kvh, b, pol);
       if (kDbg && it == 0 && lane == 0) dbg_stamp(p, 15);
       mbar_wait(vempty(st), par);
       if (lane == 0) mbar_arrive_expect_tx(vfull(st), (uint32_t)nbox * kTcBoxBytes);
       __syncwarp();
-      if (lane >= 8 && lane < 16 && c < nbox) tma_load_4d(v_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_v, vfull(st), 0, row0, kvh, b, pol);
+      if (lane >= 8 && lane < 16 && issue) tma_load_4d(v_base + st * kTcTileBytes + c * kTcBoxBytes, &tm_v, vfull(st), 0, row0, kvh, b, pol);
       if (kDbg && it == 0 && lane == 0) dbg_stamp(p, 2);
       if (it == 0 && p.cluster > 1) { cluster_arrive_release(); cl_arrived = true; }
       ++it;

@@ -630,7 +630,7 @@ __global__ void __launch_bounds__(256) prefill_plan_kernel(const int32_t* __rest
 }
 
 int encode_kv_tensor_map(CUtensorMap* tm, const void* base, int kv_dtype, int64_t stride_block, int64_t stride_slot,
-                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D);
+                         int64_t stride_head, int64_t num_blocks, int block_size, int Hkv, int D, int box_tokens = kChunkTokens);
 int launch_with_pdl(const void* func, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, void** args);
 unsigned long long* option_debug_buffer();
 int option_debug();

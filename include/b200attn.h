@@ -431,7 +431,8 @@ B200ATTN_API int b200attn_kv_gather(const void* const* k_planes, const void* con
  * Runtime knobs (host, process-wide): "pdl" (programmatic dependent launch, default 1), "tc" (tcgen05 consumer for
  * fp8 KV with group size <= 8, default 1), "cluster" (thread-block cluster size of that kernel: partials of a split
  * pair whose CTAs share a cluster are merged through distributed shared memory; default 2, 1 = off), "fused_write"
- * (b200attn_decode_kv_write stores the new token inside the decode kernel when the shape allows, default 1).
+ * (b200attn_decode_kv_write stores the new token inside the decode kernel when the shape allows, default 1), "big_box"
+ * (tcgen05 decode: one TMA box per min(block_size, 64) tokens instead of one per 16, default 1).
  * Returns the previous value or B200ATTN_EINVAL for an unknown name.
  */
 B200ATTN_API int b200attn_set_option(const char* name, int32_t value);

@@ -114,7 +114,9 @@ LADDER = [
     ("fp8_fp16_act", [300, 700], 16, 2, "fp8", "fp16", 5, {}),
     ("fp8_NHD_layout", [300, 700], 16, 2, "fp8", "bf16", 5, {"layout": "NHD"}),
     ("fp8_block32", [300, 700], 16, 2, "fp8", "bf16", 5, {"bs": 32}),
+    ("fp8_block64", [300, 700, 1, 65], 16, 2, "fp8", "bf16", 5, {"bs": 64}),
     ("fp8_block128", [300, 700], 16, 2, "fp8", "bf16", 5, {"bs": 128}),
+    ("fp8_block256", [300, 700, 257], 16, 2, "fp8", "bf16", 5, {"bs": 256}),
     ("fp8_heavy_tail_saturation", [300, 700], 16, 2, "fp8", "bf16", 5, {"dist": "heavy"}),
     ("bf16_L64", [64], 8, 1, "bf16", "bf16", 1, {}),
     ("bf16_L37", [37], 8, 1, "bf16", "bf16", 1, {}),

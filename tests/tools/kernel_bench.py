@@ -21,11 +21,11 @@ def main():
     ap.add_argument("--Hq", type=int, default=16); ap.add_argument("--Hkv", type=int, default=2)
     ap.add_argument("--kv", default="fp8"); ap.add_argument("--layers", type=int, default=8)
     ap.add_argument("--ctas", default="0"); ap.add_argument("--debug", default="0"); ap.add_argument("--pdl", type=int, default=0)
-    ap.add_argument("--tc", type=int, default=1); ap.add_argument("--graph", type=int, default=0); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--ragged", type=int, default=0)
+    ap.add_argument("--tc", type=int, default=1); ap.add_argument("--graph", type=int, default=0); ap.add_argument("--reps", type=int, default=5); ap.add_argument("--ragged", type=int, default=0); ap.add_argument("--bs", type=int, default=16)
     a = ap.parse_args()
     dev = torch.device("cuda")
     lib = ops.load_library()
-    B, L, Hq, Hkv, D, bs = a.B, a.L, a.Hq, a.Hkv, 128, 16
+    B, L, Hq, Hkv, D, bs = a.B, a.L, a.Hq, a.Hkv, 128, a.bs
     fp8 = a.kv == "fp8"
     kv_t = torch.uint8 if fp8 else torch.bfloat16
     rng = np.random.default_rng(7)
