@@ -307,8 +307,13 @@ class PluginStep:
                                           num_actual_tokens=B, max_query_len=1, max_seq_len=int(P.lens_np.max()),
                                           block_table_tensor=P.bt, slot_mapping=P.step_slots)
         self.md = self.builder.build(0, self.cm)
-        self.q2 = P.q.view(P.NL, B, Hq * D); self.k2 = P.kn.view(P.NL, B, Hkv * D); self.v2 = P.vn.view(P.NL, B, Hkv * D)
+        self.use_inputs(P.q, P.kn, P.vn)
         self.o2 = P.out.view(P.NL, B, Hq * D)
+
+    def use_inputs(self, q, kn, vn):
+        """[NL, B, H, D] tensors (or views of one packed qkv activation, as vLLM's qkv split hands them over)"""
+        NL, B = self.P.NL, self.B
+        self.q2 = q.view(NL, B, self.Hq * self.D); self.k2 = kn.view(NL, B, self.Hkv * self.D); self.v2 = vn.view(NL, B, self.Hkv * self.D)
 
     def build(self):
         self.md = self.builder.build(0, self.cm)   # eager, before every step / replay -- as vLLM does
@@ -333,7 +338,11 @@ class OpsStep:
         w = P.w
         self.P = P
         self.ws = ops.DecodeWorkspace(dev, w["B"], P.kv_t, head_dim=w["D"], group_size=w["Hq"] // w["Hkv"])
+        self.use_inputs(P.q, P.kn, P.vn)
         self.build()
+
+    def use_inputs(self, q, kn, vn):
+        self.q, self.kn, self.vn = q, kn, vn
 
     def build(self):
         w = self.P.w
@@ -345,8 +354,8 @@ class OpsStep:
         P = self.P
         for l in range(lo, P.NL if hi is None else hi):
             kc, vc = P.planes[l]
-            torch.ops.b200attn.kv_write(P.kn[l], P.vn[l], kc, vc, P.step_slots, P.k_scale, P.v_scale)
-            self.ws.decode(P.q[l], kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale, P.sm_scale, fresh_tokens=1)
+            torch.ops.b200attn.kv_write(self.kn[l], self.vn[l], kc, vc, P.step_slots, P.k_scale, P.v_scale)
+            self.ws.decode(self.q[l], kc, vc, P.bt, P.lens, P.out[l], P.k_scale, P.v_scale, P.sm_scale, fresh_tokens=1)
 
     @property
     def grid(self):
@@ -434,56 +443,91 @@ def run_ours(args, w):
                "p90_ms": float(np.percentile(per, 90)), "note": "each step bracketed by its own CUDA events (serialises host enqueue and device)"}
 
     # ---- (2) end-to-end: host inputs -> pinned H2D -> build + layer hooks -> D2H of the attention output, every step ----
-    h_q, h_kn, h_vn = P.q.cpu().pin_memory(), P.kn.cpu().pin_memory(), P.vn.cpu().pin_memory()
+    # The step's activations sit in host memory the way the model produces them: one packed qkv row per token and layer
+    # ([T, (Hq + 2 Hkv) * D], $VLLM/model_executor/models/qwen3.py:153 `qkv.split`), so a layer group is ONE H2D copy and the
+    # hooks read q / k / v as strided views of it -- every copy node of a graph costs ~7 us of DMA set-up on this box.
+    h_qkv = torch.cat([P.q, P.kn, P.vn], dim=2).cpu().pin_memory()
+    d_qkv = torch.empty(h_qkv.shape, dtype=h_qkv.dtype, device=dev)
+    S.use_inputs(d_qkv[:, :, :Hq], d_qkv[:, :, Hq:Hq + Hkv], d_qkv[:, :, Hq + Hkv:])
     h_slots, h_lens, h_bt = P.step_slots.cpu().pin_memory(), P.lens.cpu().pin_memory(), P.bt.cpu().pin_memory()
     h_out = torch.empty(P.out.shape, dtype=P.out.dtype).pin_memory()
-    h2d_bytes = sum(t.numel() * t.element_size() for t in (h_q, h_kn, h_vn, h_slots, h_lens, h_bt))
+    h2d_bytes = sum(t.numel() * t.element_size() for t in (h_qkv, h_slots, h_lens, h_bt))
     d2h_bytes = h_out.numel() * h_out.element_size()
-    # The layer part is pipelined in layer groups: group g's q/k/v travel H2D on a copy stream while group g-1 computes, and
-    # its outputs travel D2H on a second copy stream while group g+1 computes (PCIe is full duplex); the whole call is one
-    # CUDA graph with three stream branches.
-    NG = int(os.environ.get("B200_E2E_GROUPS", "5"))
-    NG = NG if (NG > 0 and NL % NG == 0) else 1
-    GL = NL // NG
+    # The layer part is pipelined in layer groups: group g's q/k/v travel H2D on a copy stream while earlier groups compute, and
+    # its outputs travel D2H on a second copy stream while later groups compute (PCIe is full duplex); the whole call is one
+    # CUDA graph with three stream branches.  The input branch forks right after the metadata copies, beside build().
+    # B200_E2E_GROUPS = a group count (equal sizes) or a comma list of group sizes.
+    def group_sizes(spec):
+        if "," in spec:
+            sizes = [int(x) for x in spec.split(",")]
+            return sizes if (sum(sizes) == NL and min(sizes) > 0) else [NL]
+        if spec:
+            n = int(spec)
+            return [NL // n] * n if (n > 0 and NL % n == 0) else [NL]
+        if NL < 12:
+            return [NL]
+        # short first and last groups: the first group's H2D and the last group's D2H are the only copies nothing hides
+        # (c2, 20 layers: 5 x 4 -> 623 us, [1, 3, 4, 4, 4, 3, 1] -> 614 us, 10 x 2 -> 646 us, one group -> 772 us per step)
+        mid = NL - 8
+        return [1, 3] + [4] * (mid // 4) + ([mid % 4] if mid % 4 else []) + [3, 1]
+
     s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
 
-    def e2e_body():
-        # step metadata first (build() reads it), then build() -- capture-safe: two small copies + the device-side plan -- then
-        # the layer groups
-        P.step_slots.copy_(h_slots, non_blocking=True); P.lens.copy_(h_lens, non_blocking=True); P.bt.copy_(h_bt, non_blocking=True)
-        S.build()
-        main = torch.cuda.current_stream()
-        s_in.wait_stream(main)
-        s_out.wait_stream(main)
-        ev_in = []
-        with torch.cuda.stream(s_in):
-            for gi in range(NG):
-                sl = slice(gi * GL, (gi + 1) * GL)
-                P.q[sl].copy_(h_q[sl], non_blocking=True); P.kn[sl].copy_(h_kn[sl], non_blocking=True); P.vn[sl].copy_(h_vn[sl], non_blocking=True)
-                ev = torch.cuda.Event(); ev.record(s_in); ev_in.append(ev)
-        for gi in range(NG):
-            main.wait_event(ev_in[gi])
-            S.layers(gi * GL, (gi + 1) * GL)
-            ev = torch.cuda.Event(); ev.record(main)
-            with torch.cuda.stream(s_out):
-                s_out.wait_event(ev)
-                sl = slice(gi * GL, (gi + 1) * GL)
-                h_out[sl].copy_(P.out[sl], non_blocking=True)
-        main.wait_stream(s_in)
-        main.wait_stream(s_out)
+    def make_e2e_body(sizes):
+        bounds = [0]
+        for n in sizes:
+            bounds.append(bounds[-1] + n)
 
-    e2e_replay, e2e_graphed = (e2e_body, False)
-    if use_graph and gathered is None:
-        e2e_replay, e2e_graphed = capture(e2e_body, side)
+        def e2e_body():
+            main = torch.cuda.current_stream()
+            # step metadata first (build() reads it; the copy engine serves requests in order), then the qkv copies on their
+            # own branch beside build() -- capture-safe: small copies + the device-side plan
+            P.step_slots.copy_(h_slots, non_blocking=True); P.lens.copy_(h_lens, non_blocking=True); P.bt.copy_(h_bt, non_blocking=True)
+            s_in.wait_stream(main)
+            ev_in = []
+            with torch.cuda.stream(s_in):
+                for gi in range(len(sizes)):
+                    sl = slice(bounds[gi], bounds[gi + 1])
+                    d_qkv[sl].copy_(h_qkv[sl], non_blocking=True)
+                    ev = torch.cuda.Event(); ev.record(s_in); ev_in.append(ev)
+            S.build()
+            s_out.wait_stream(main)
+            for gi in range(len(sizes)):
+                main.wait_event(ev_in[gi])
+                S.layers(bounds[gi], bounds[gi + 1])
+                ev = torch.cuda.Event(); ev.record(main)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(ev)
+                    sl = slice(bounds[gi], bounds[gi + 1])
+                    h_out[sl].copy_(P.out[sl], non_blocking=True)
+            main.wait_stream(s_in)
+            main.wait_stream(s_out)
+        return e2e_body
 
-    def e2e_step():
-        e2e_replay()
-        torch.cuda.current_stream().synchronize()   # the caller consumes the result every step
+    def measure_e2e(sizes):
+        body = make_e2e_body(sizes)
+        replay, graphed = (body, False)
+        if use_graph and gathered is None:
+            replay, graphed = capture(body, side)
 
-    for _ in range(max(3, args.warmup)):
-        e2e_step()
-    ms_e2e = max_over_ranks(time_region(e2e_step, args.steps, barrier), dev, world)
+        def e2e_step():
+            replay()
+            torch.cuda.current_stream().synchronize()   # the caller consumes the result every step
+
+        for _ in range(max(3, args.warmup)):
+            e2e_step()
+        return max_over_ranks(time_region(e2e_step, args.steps, barrier), dev, world), graphed
+
+    if os.environ.get("B200_E2E_SWEEP"):   # tuning aid: "5;20;1,1,4,4,4,4,1,1;..." -> one stderr line per schedule
+        for spec in os.environ["B200_E2E_SWEEP"].split(";"):
+            ms_try, _ = measure_e2e(group_sizes(spec))
+            if rank == 0:
+                print(f"[e2e sweep] groups {group_sizes(spec)}: {ms_try / args.steps * 1e3:.1f} us/step", file=sys.stderr, flush=True)
+    e2e_sizes = group_sizes(os.environ.get("B200_E2E_GROUPS", ""))
+    NG = len(e2e_sizes)
+    ms_e2e, e2e_graphed = measure_e2e(e2e_sizes)
     ms_e2e_per_step = ms_e2e / args.steps
+    S.use_inputs(P.q, P.kn, P.vn)
 
     # ---- (3) roofline leg: the decode kernel alone, NL launches over the NL distinct layer caches, one CUDA graph ----
     ws = ops.DecodeWorkspace(dev, B, P.kv_t, head_dim=D, group_size=Hq // Hkv)
@@ -592,7 +636,7 @@ def run_ours(args, w):
         "distribution": dist_ms,
         "e2e": {"value": gbs_e2e, "unit": "GB/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                 "ms_per_step": ms_e2e_per_step, "tok_s": B / (ms_e2e_per_step * 1e-3), "api": api,
-                "pipeline": (f"one CUDA graph: metadata H2D, build(), then {NG} layer groups with H2D / layer hooks / D2H on three stream branches"
+                "pipeline": (f"one CUDA graph: metadata H2D, build() beside the first packed-qkv H2D, then {NG} layer groups of {e2e_sizes} layers with H2D / layer hooks / D2H on three stream branches"
                              if e2e_graphed else "metadata H2D, build(), copies and layer hooks issued eagerly")},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "achieved": kern_gbs, "peak": peak, "unit": "GB/s", "frac": kern_gbs / peak,
