@@ -32,16 +32,38 @@ namespace b200attn {
 #define B200_PF_PTMEM 1   // P (hi, lo) as the TMEM-resident A operand of the second GEMM (0: staged in shared memory)
 #endif
 #ifndef B200_PF_HALF2
-#define B200_PF_HALF2 1   // probabilities in f16x2 from the exponent on (0: the fp32 / integer-rounding path of the first version)
+#define B200_PF_HALF2 1   // probabilities in f16x2 from the exponent on (0: the fp32 / integer-rounding path of the first version;
+                          // 2: exponent in fp32, hi from the fp32 pair -- 5 % slower than 1)
 #endif
-constexpr int kPfThreads = 320;
-constexpr int kPfSoftmaxThreads = 256;
-constexpr int kPfProducerWarp = 8, kPfMmaWarp = 9;
+#ifndef B200_PF_SPLIT
+#define B200_PF_SPLIT 2   // softmax threads per query row (2 or 4; 4 = 16 softmax warps measured 8 % slower: 707 vs 656 us on the 8k prefill)
+#endif
+constexpr int kPfSplit = B200_PF_SPLIT;
+constexpr int kPfCols = 128 / kPfSplit;       // S columns / head dims per softmax thread
+constexpr int kPfSoftmaxThreads = 128 * kPfSplit;
+constexpr int kPfSoftmaxWarps = kPfSoftmaxThreads / 32;
+constexpr int kPfThreads = kPfSoftmaxThreads + 64;
+constexpr int kPfProducerWarp = kPfSoftmaxWarps, kPfMmaWarp = kPfSoftmaxWarps + 1;
+static_assert(kPfSplit == 2 || kPfSplit == 4, "two or four threads per query row");
 constexpr int kPfTile = 128;                  // kv tokens per tile = query rows per tile
-constexpr int kPfStages = 3;
+#ifndef B200_PF_CTAS2
+#define B200_PF_CTAS2 0   // 1: two CTAs per SM, S single-buffered with P aliased onto it (256 TMEM columns), 2-stage K / V rings --
+                          // measured 46 % SLOWER (8k prefill 667 -> 974 us): kept as an experiment switch, see DESIGN.md 3.5
+#endif
+#if B200_PF_CTAS2 && !B200_PF_PTMEM
+#error "B200_PF_CTAS2 needs the TMEM-resident P operand"
+#endif
+constexpr int kPfCtasPerSm = B200_PF_CTAS2 ? 2 : 1;
+constexpr int kPfStages = B200_PF_CTAS2 ? 2 : 3;
+constexpr int kPfSBufs = B200_PF_CTAS2 ? 1 : 2;           // S (and P) buffers in TMEM
 constexpr int kPfTileBytes = kPfTile * kD;    // 16 KiB (fp8)
 constexpr int kPfBoxBytes = kChunkTokens * kD;
-constexpr int kPfTmemCols = 512;              // S0 [0,128) S1 [128,256) O [256,384)
+// TMEM columns.  One CTA per SM: S0 [0,128) S1 [128,256) O [256,384) P0 P1 [384,512).  Two CTAs per SM: S [0,128), P (hi 32 +
+// lo 32 columns) written over S once every softmax thread has its logits in registers, O [128,256): the chain
+// QK(j) -> softmax(j) -> PV(j) -> QK(j+1) of one CTA is serial and the SM's other CTA fills its gaps (and hides the ~12k
+// cycles of per-CTA prologue + epilogue: query load and split, pipeline fill, output store).
+constexpr int kPfTmemCols = B200_PF_CTAS2 ? 256 : 512;
+constexpr int kPfColS = 0, kPfColO = B200_PF_CTAS2 ? 128 : 256, kPfColP = B200_PF_CTAS2 ? 0 : 384;
 constexpr float kPfMargin = 4.0f;             // the row maximum is raised when a logit exceeds it by 2^4
 constexpr float kPfShift = 4.0f;              // p' = p * 2^4 <= 2^8 < 448
 
@@ -50,12 +72,12 @@ struct PfSmem {
   static constexpr int kK = kQ + 2 * kPfTileBytes;
   static constexpr int kV = kK + kPfStages * kPfTileBytes;
   static constexpr int kP = kV + kPfStages * kPfTileBytes;       // [2 buffers][hi, lo]
-  static constexpr int kXch = kP + 4 * kPfTileBytes;             // float [2 slots][2 halves][128 rows]: row max / sum exchange
-  static constexpr int kBars = kXch + 2 * 2 * 128 * 4;
+  static constexpr int kXch = kP + (B200_PF_PTMEM ? 0 : 4 * kPfTileBytes);             // float [2 slots][kPfSplit parts][128 rows]: row max / sum exchange
+  static constexpr int kBars = kXch + 2 * kPfSplit * 128 * 4;
   static constexpr int kNumBars = 4 * kPfStages + 10;
   static constexpr int kTmemPtr = kBars + kNumBars * 8;
   static constexpr int kTotal = kTmemPtr + 16;
-  static_assert(kTotal <= 227 * 1024, "smem budget exceeded");
+  static_assert(kTotal <= 227 * 1024 / kPfCtasPerSm - 1024, "smem budget exceeded");
 };
 
 struct PrefillParams {
@@ -75,7 +97,7 @@ struct PrefillParams {
   int num_reqs, Hq, Hv, G, gsplit, cpb, tpt;
   int tok0;                        // query_start_loc[0] of the slice (token index subtracted from every offset)
   unsigned long long* dbg;         // per-CTA wait-cycle counters [grid][16] (debug builds of the launch only)
-  int variant;                     // debug instantiation only: 1 = softmax warps skip their arithmetic, 2 = no PV MMAs, 3 = hi terms only
+  int variant;                     // debug instantiation only, bit flags: 1 = softmax warps skip their arithmetic, 2 = no PV MMAs, 4 = hi terms only, 8 = no QK MMAs
 };
 
 __device__ __forceinline__ void pf_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -102,6 +124,15 @@ __device__ __forceinline__ void pf_st16_nowait(uint32_t taddr, const uint32_t (&
       ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
         "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
+}
+__device__ __forceinline__ void pf_st_nowait(uint32_t taddr, const uint32_t (&r)[16]) { pf_st16_nowait(taddr, r); }
+__device__ __forceinline__ void pf_st_nowait(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void pf_st_nowait(uint32_t taddr, const uint32_t (&r)[4]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]) : "memory");
 }
 __device__ __forceinline__ void pf_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -175,7 +206,7 @@ __device__ __forceinline__ void pf_split4_pos(const float (&pv)[4], uint32_t& hi
 __device__ __forceinline__ uint32_t pf_swz(int r, int c) { return (uint32_t)r * 128u + (uint32_t)((c ^ (r & 7)) << 4); }
 
 template <int QDT, bool kDbg>
-__global__ void __launch_bounds__(kPfThreads, 1)
+__global__ void __launch_bounds__(kPfThreads, kPfCtasPerSm)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v, const PrefillParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);
@@ -229,10 +260,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       mbar_init(kfull(i), 1); mbar_init(kempty(i), 1);
       mbar_init(vfull(i), 1); mbar_init(vempty(i), 1);
     }
-    mbar_init(qfull, 8);
+    mbar_init(qfull, kPfSoftmaxWarps);
     for (int i = 0; i < 2; ++i) {
-      mbar_init(sfull(i), 1); mbar_init(sempty(i), 8);
-      mbar_init(pfull(i), 8); mbar_init(pempty(i), 1);
+      mbar_init(sfull(i), 1); mbar_init(sempty(i), kPfSoftmaxWarps);
+      mbar_init(pfull(i), kPfSoftmaxWarps); mbar_init(pempty(i), 1);
     }
     mbar_fence_init();
     prefetch_tensormap(&tm_k);
@@ -285,16 +316,17 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     } else if (warp == kPfMmaWarp) {
       // =========================================== MMA issuer ===========================================
       auto issue_qk = [&](int j) {
-        const uint32_t b = j & 1, st = j % kPfStages;
+        const uint32_t b = j % kPfSBufs, st = j % kPfStages;
         wait_t(kfull(st), (j / kPfStages) & 1, 0);
-        wait_t(sempty(b), ((j >> 1) & 1) ^ 1, 1);
+        wait_t(sempty(b), ((j / kPfSBufs) & 1) ^ 1, 1);
         pf_fence_after();
         if (lane == 0) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
+            if (kDbg && (p.variant & 8)) break;
             const uint64_t db = pf_desc(k_base + st * kPfTileBytes + k * 32, 16, 1024);
-            pf_mma_f8(tmem + b * 128, pf_desc(q_base + k * 32, 16, 1024), db, kPfIdescQK, k > 0);
-            if (!kDbg || p.variant != 3) pf_mma_f8(tmem + b * 128, pf_desc(q_base + kPfTileBytes + k * 32, 16, 1024), db, kPfIdescQK, 1u);
+            pf_mma_f8(tmem + kPfColS + b * 128, pf_desc(q_base + k * 32, 16, 1024), db, kPfIdescQK, k > 0);
+            if (!kDbg || !(p.variant & 4)) pf_mma_f8(tmem + kPfColS + b * 128, pf_desc(q_base + kPfTileBytes + k * 32, 16, 1024), db, kPfIdescQK, 1u);
           }
           pf_commit(kempty(st));
           pf_commit(sfull(b));
@@ -302,22 +334,22 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         __syncwarp();
       };
       auto issue_pv = [&](int j) {
-        const uint32_t b = j & 1, st = j % kPfStages;
+        const uint32_t b = j % kPfSBufs, st = j % kPfStages;
         wait_t(vfull(st), (j / kPfStages) & 1, 2);
-        wait_t(pfull(b), (j >> 1) & 1, 3);
+        wait_t(pfull(b), (j / kPfSBufs) & 1, 3);
         pf_fence_after();
         if (lane == 0) {
           const int nk = (min(kPfTile, kv_end - j * kPfTile) + 31) >> 5;
           for (int k = 0; k < nk; ++k) {
-            if (kDbg && p.variant == 2) break;
+            if (kDbg && (p.variant & 2)) break;
             const uint64_t db = pf_desc(v_base + st * kPfTileBytes + k * 4096, 0, 1024);
 #if B200_PF_PTMEM
-            // P lives in TMEM columns [384, 512): buffer b = 64 columns (32 hi + 32 lo), a 32-token K step = 8 columns
-            pf_mma_f8_ts(tmem + 256, tmem + 384 + b * 64 + k * 8, db, kPfIdescPV, (j > 0 || k > 0) ? 1u : 0u);
-            if (!kDbg || p.variant != 3) pf_mma_f8_ts(tmem + 256, tmem + 384 + b * 64 + 32 + k * 8, db, kPfIdescPV, 1u);
+            // P lives in TMEM: buffer b = 64 columns (32 hi + 32 lo) from kPfColP on, a 32-token K step = 8 columns
+            pf_mma_f8_ts(tmem + kPfColO, tmem + kPfColP + b * 64 + k * 8, db, kPfIdescPV, (j > 0 || k > 0) ? 1u : 0u);
+            if (!kDbg || !(p.variant & 4)) pf_mma_f8_ts(tmem + kPfColO, tmem + kPfColP + b * 64 + 32 + k * 8, db, kPfIdescPV, 1u);
 #else
-            pf_mma_f8(tmem + 256, pf_desc(p_base + (2 * b) * kPfTileBytes + k * 32, 16, 1024), db, kPfIdescPV, (j > 0 || k > 0) ? 1u : 0u);
-            if (!kDbg || p.variant != 3) pf_mma_f8(tmem + 256, pf_desc(p_base + (2 * b + 1) * kPfTileBytes + k * 32, 16, 1024), db, kPfIdescPV, 1u);
+            pf_mma_f8(tmem + kPfColO, pf_desc(p_base + (2 * b) * kPfTileBytes + k * 32, 16, 1024), db, kPfIdescPV, (j > 0 || k > 0) ? 1u : 0u);
+            if (!kDbg || !(p.variant & 4)) pf_mma_f8(tmem + kPfColO, pf_desc(p_base + (2 * b + 1) * kPfTileBytes + k * 32, 16, 1024), db, kPfIdescPV, 1u);
 #endif
           }
           pf_commit(vempty(st));
@@ -329,14 +361,19 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         mbar_wait(qfull, 0);
         issue_qk(0);
         for (int j = 0; j < n_kv; ++j) {
+#if B200_PF_CTAS2
+          issue_pv(j);                         // P(j) sits where S(j) was: the next QK may only follow this PV (the tensor
+          if (j + 1 < n_kv) issue_qk(j + 1);   // pipe executes in issue order)
+#else
           if (j + 1 < n_kv) issue_qk(j + 1);   // QK of the next tile runs while the softmax warps work on this one
           issue_pv(j);
+#endif
         }
       }
     } else {
       // =========================================== softmax warps ===========================================
-      const int tid = threadIdx.x;                       // 0..255
-      const int row = tid & 127, half = tid >> 7;        // query row of the tile (= TMEM lane) and 64-column half of it
+      const int tid = threadIdx.x;                       // 0..kPfSoftmaxThreads-1
+      const int row = tid & 127, part = tid >> 7;        // query row of the tile (= TMEM lane) and which kPfCols columns of it
       const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
       const float ninf = -INFINITY;
       const bool row_ok = row < rows;
@@ -345,13 +382,19 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       using E = Elem<QDT>;
       float* xch = reinterpret_cast<float*>(smem_raw + PfSmem::kXch);
       int xs = 0;
-      // value of the other half-row's thread: write, barrier over the 256 softmax threads, read (alternating slots)
-      auto exchange = [&](float v) {
-        xch[(xs * 2 + half) * 128 + row] = v;
+      // the row's other threads' values combined (maximum or sum): write, barrier over the softmax threads, read
+      // (alternating slots)
+      auto exchange = [&](float v, bool sum) {
+        xch[(xs * kPfSplit + part) * 128 + row] = v;
         const long long t0 = kDbg ? clock64() : 0;
         named_bar_sync(1, kPfSoftmaxThreads);
         if (kDbg) acc[2] += clock64() - t0;
-        const float o = xch[(xs * 2 + (half ^ 1)) * 128 + row];
+        float o = sum ? 0.f : -INFINITY;
+#pragma unroll
+        for (int i = 1; i < kPfSplit; ++i) {
+          const float x = xch[(xs * kPfSplit + ((part + i) & (kPfSplit - 1))) * 128 + row];
+          o = sum ? o + x : fmaxf(o, x);
+        }
         xs ^= 1;
         return o;
       };
@@ -359,19 +402,19 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       float crow;
       {
         const uint16_t* src = reinterpret_cast<const uint16_t*>(p.q) + (int64_t)(q0 + t) * p.q_stride_t +
-                              (int64_t)(hv * p.G + g) * p.q_stride_h + half * 64;
-        uint4 raw[8];
+                              (int64_t)(hv * p.G + g) * p.q_stride_h + part * kPfCols;
+        uint4 raw[kPfCols / 8];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) raw[c] = row_ok ? __ldcg(reinterpret_cast<const uint4*>(src) + c) : make_uint4(0u, 0u, 0u, 0u);
+        for (int c = 0; c < kPfCols / 8; ++c) raw[c] = row_ok ? __ldcg(reinterpret_cast<const uint4*>(src) + c) : make_uint4(0u, 0u, 0u, 0u);
         float amax = 0.f;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < kPfCols / 8; ++c) {
           const uint32_t w[4] = {raw[c].x, raw[c].y, raw[c].z, raw[c].w};
 #pragma unroll
           for (int i = 0; i < 4; ++i)
             amax = fmaxf(amax, fmaxf(fabsf(q_to_float<QDT>(w[i] & 0xffff)), fabsf(q_to_float<QDT>(w[i] >> 16))));
         }
-        amax = fmaxf(amax, exchange(amax));
+        amax = fmaxf(amax, exchange(amax, false));
         const uint32_t eb = (__float_as_uint(amax) >> 23) & 0xffu;
         const bool norm = eb >= 16 && eb < 255;
         const float inv = norm ? __uint_as_float((261u - eb) << 23) : 1.0f;   // row maximum -> [128, 256)
@@ -379,7 +422,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         const float kscale = __ldg(p.k_scale + (int64_t)kvh * p.scale_stride);
         crow = fct * p.sm_scale_log2 * kscale;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {   // 16 head dims -> one 16-byte chunk of each operand row
+        for (int c = 0; c < kPfCols / 16; ++c) {   // 16 head dims -> one 16-byte chunk of each operand row
           uint32_t hi[8], lo[8];
 #pragma unroll
           for (int hlf = 0; hlf < 2; ++hlf) {
@@ -389,7 +432,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             for (int i = 0; i < 4; ++i)
               pf_split_pair(q_to_float<QDT>(w[i] & 0xffff) * inv, q_to_float<QDT>(w[i] >> 16) * inv, hi[hlf * 4 + i], lo[hlf * 4 + i]);
           }
-          const uint32_t a = q_base + pf_swz(row, half * 4 + c);
+          const uint32_t a = q_base + pf_swz(row, part * (kPfCols / 16) + c);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(hi[0] | (hi[1] << 16)), "r"(hi[2] | (hi[3] << 16)),
                        "r"(hi[4] | (hi[5] << 16)), "r"(hi[6] | (hi[7] << 16)) : "memory");
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a + kPfTileBytes), "r"(lo[0] | (lo[1] << 16)), "r"(lo[2] | (lo[3] << 16)),
@@ -402,41 +445,42 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 
       float m_run = ninf, l_run = 0.f;
       for (int j = 0; j < n_kv; ++j) {
-        const uint32_t b = j & 1;
-        const int col0 = j * kPfTile + half * 64;            // cache position of this thread's first column
-        const bool need_mask = col0 + 64 > limit;
-        wait_t(sfull(b), (j >> 1) & 1, 0);
+        const uint32_t b = j % kPfSBufs, bpar = (j / kPfSBufs) & 1;
+        const int col0 = j * kPfTile + part * kPfCols;       // cache position of this thread's first column
+        const bool need_mask = col0 + kPfCols > limit;
+        wait_t(sfull(b), bpar, 0);
         pf_fence_after();
-        if (kDbg && p.variant == 1) {
+        if (kDbg && (p.variant & 1)) {
           pf_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(sempty(b));
-          wait_t(pempty(b), ((j >> 1) & 1) ^ 1, 1);
+          wait_t(pempty(b), bpar ^ 1, 1);
           pf_fence_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(pfull(b));
           continue;
         }
         // ---- the half row of logits: one TMEM read, kept in registers ----
-        uint32_t sr[64];
-        pf_ld32(tmem + lane_base + b * 128 + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&sr[0]));
-        pf_ld32(tmem + lane_base + b * 128 + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[32]));
+        uint32_t sr[kPfCols];
+#pragma unroll
+        for (int cc = 0; cc < kPfCols / 32; ++cc)
+          pf_ld32(tmem + lane_base + kPfColS + b * 128 + part * kPfCols + cc * 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[cc * 32]));
         pf_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(sempty(b));               // S is in registers: the QK of tile j + 2 may overwrite it
         float mx = ninf;
         if (need_mask) {
 #pragma unroll
-          for (int i = 0; i < 64; ++i) {
+          for (int i = 0; i < kPfCols; ++i) {
             if (col0 + i >= limit) sr[i] = 0xff800000u;      // -inf (crow > 0); also replaces whatever stale K rows produced
             mx = fmaxf(mx, __uint_as_float(sr[i]));
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < 64; ++i) mx = fmaxf(mx, __uint_as_float(sr[i]));
+          for (int i = 0; i < kPfCols; ++i) mx = fmaxf(mx, __uint_as_float(sr[i]));
         }
         mx *= crow;
-        mx = fmaxf(mx, exchange(mx));
+        mx = fmaxf(mx, exchange(mx, false));
         // ---- raise the running maximum lazily (always on the first tile); O is rescaled in TMEM ----
         const bool raise = mx > m_run + kPfMargin;
         if (__any_sync(0xffffffffu, raise)) {
@@ -445,27 +489,27 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           l_run *= fac;
           m_run = m_new;
           if (j > 0) {
-            mbar_wait(pempty((j - 1) & 1), ((j - 1) >> 1) & 1);   // every PV issued so far has completed
+            mbar_wait(pempty((j - 1) % kPfSBufs), ((j - 1) / kPfSBufs) & 1);   // every PV issued so far has completed
             pf_fence_after();
 #pragma unroll 1
-            for (int cc = 0; cc < 2; ++cc) {
+            for (int cc = 0; cc < kPfCols / 32; ++cc) {
               uint32_t o[32];
-              pf_ld32(tmem + lane_base + 256 + half * 64 + cc * 32, o);
+              pf_ld32(tmem + lane_base + kPfColO + part * kPfCols + cc * 32, o);
 #pragma unroll
               for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * fac);
-              pf_st32(tmem + lane_base + 256 + half * 64 + cc * 32, o);
+              pf_st32(tmem + lane_base + kPfColO + part * kPfCols + cc * 32, o);
             }
             pf_fence_before();
           }
         }
         // ---- p' = 2^(x - m + 4), row sum, hi / lo split, A-operand rows of the second GEMM ----
-        wait_t(pempty(b), ((j >> 1) & 1) ^ 1, 1);   // PV of tile j-2 no longer reads this P buffer
+        wait_t(pempty(b), bpar ^ 1, 1);   // the PV that last read this P buffer has completed
         const float off = kPfShift - m_run;
-#if B200_PF_PTMEM
-        uint32_t hw[16], lw[16];                    // this thread's 64 tokens of the row: hi bytes, lo bytes
+#if B200_PF_PTMEM && !B200_PF_CTAS2
+        uint32_t hw[kPfCols / 4], lw[kPfCols / 4];  // this thread's kPfCols tokens of the row: hi bytes, lo bytes
 #endif
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {               // 16 tokens -> one 16-byte chunk of each operand row
+        for (int c = 0; c < kPfCols / 16; ++c) {    // 16 tokens -> one 16-byte chunk of each operand row
           uint32_t h4[4], l4[4];
 #if B200_PF_HALF2
           // two elements per instruction from the exponent on: t = x crow + off in fp32, packed to f16x2 (|t| < 16 wherever p'
@@ -479,11 +523,20 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             for (int q2 = 0; q2 < 2; ++q2) {
               const float t0 = fmaf(__uint_as_float(sr[c * 16 + w * 4 + 2 * q2]), crow, off);
               const float t1 = fmaf(__uint_as_float(sr[c * 16 + w * 4 + 2 * q2 + 1]), crow, off);
-              uint32_t t2, p2, back, d2;
+              uint32_t p2, back, d2;
               uint16_t hi2, lo2;
+#if B200_PF_HALF2 == 2
+              // exponent in fp32 (ex2.approx.f16x2 is two scalar MUFUs plus byte permutes anyway), hi straight from the fp32
+              // pair, p' packed to f16x2 only for the lo term and the row sum
+              const float p0 = fast_exp2(t0), p1 = fast_exp2(t1);
+              asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi2) : "f"(p1), "f"(p0));
+              asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(p2) : "f"(p1), "f"(p0));
+#else
+              uint32_t t2;
               asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(t2) : "f"(t1), "f"(t0));
               asm("ex2.approx.f16x2 %0, %1;" : "=r"(p2) : "r"(t2));
               asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(hi2) : "r"(p2));
+#endif
               asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(back) : "h"(hi2));
               asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(d2) : "r"(p2), "r"(back));
               asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(lo2) : "r"(d2));
@@ -511,19 +564,25 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             pf_split4_pos(pv, h4[w], l4[w]);
           }
 #endif
-#if B200_PF_PTMEM
+#if B200_PF_PTMEM && B200_PF_CTAS2
+          // straight to tensor memory, 16 tokens at a time: no hi / lo staging registers (the two-CTA build has 96 per thread)
+          pf_st_nowait(tmem + lane_base + kPfColP + b * 64 + part * (kPfCols / 4) + c * 4, h4);
+          pf_st_nowait(tmem + lane_base + kPfColP + b * 64 + 32 + part * (kPfCols / 4) + c * 4, l4);
+#elif B200_PF_PTMEM
 #pragma unroll
           for (int w = 0; w < 4; ++w) { hw[c * 4 + w] = h4[w]; lw[c * 4 + w] = l4[w]; }
 #else
-          const uint32_t a = p_base + (2 * b) * kPfTileBytes + pf_swz(row, half * 4 + c);
+          const uint32_t a = p_base + (2 * b) * kPfTileBytes + pf_swz(row, part * (kPfCols / 16) + c);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(h4[0]), "r"(h4[1]), "r"(h4[2]), "r"(h4[3]) : "memory");
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a + kPfTileBytes), "r"(l4[0]), "r"(l4[1]), "r"(l4[2]), "r"(l4[3]) : "memory");
 #endif
         }
 #if B200_PF_PTMEM
         // the A operand of the second GEMM goes to tensor memory: no shared-memory write here and no shared-memory read by the MMA
-        pf_st16_nowait(tmem + lane_base + 384 + b * 64 + half * 16, hw);
-        pf_st16_nowait(tmem + lane_base + 384 + b * 64 + 32 + half * 16, lw);
+#if !B200_PF_CTAS2
+        pf_st_nowait(tmem + lane_base + kPfColP + b * 64 + part * (kPfCols / 4), hw);
+        pf_st_nowait(tmem + lane_base + kPfColP + b * 64 + 32 + part * (kPfCols / 4), lw);
+#endif
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         pf_fence_before();
 #endif
@@ -544,20 +603,20 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         if (lane == 0) mbar_arrive(pfull(b));
       }
       // ---- epilogue: O row / l -> out ----
-      l_run += exchange(l_run);
+      l_run += exchange(l_run, true);
       if (n_kv > 0) {
-        mbar_wait(pempty((n_kv - 1) & 1), ((n_kv - 1) >> 1) & 1);
+        mbar_wait(pempty((n_kv - 1) % kPfSBufs), ((n_kv - 1) / kPfSBufs) & 1);
         pf_fence_after();
       }
       const float vscale = __ldg(p.v_scale + (int64_t)kvh * p.scale_stride);
       const float onorm = (n_kv > 0 && l_run > 0.f) ? vscale / l_run : 0.f;
       typename E::type* op = reinterpret_cast<typename E::type*>(p.out) + (int64_t)(q0 + t) * p.out_stride_t +
-                             (int64_t)(hv * p.G + g) * p.out_stride_h + half * 64;
+                             (int64_t)(hv * p.G + g) * p.out_stride_h + part * kPfCols;
 #pragma unroll 1
-      for (int cc = 0; cc < 2; ++cc) {
+      for (int cc = 0; cc < kPfCols / 32; ++cc) {
         uint32_t o[32];
         if (n_kv > 0) {
-          pf_ld32(tmem + lane_base + 256 + half * 64 + cc * 32, o);
+          pf_ld32(tmem + lane_base + kPfColO + part * kPfCols + cc * 32, o);
         } else {
 #pragma unroll
           for (int i = 0; i < 32; ++i) o[i] = 0u;
@@ -752,6 +811,10 @@ extern "C" int b200attn_prefill(const void* q, int64_t q_stride_t, int64_t q_str
   const int qi = (q_dtype == B200ATTN_BF16 ? 0 : 1) + (dbg ? 2 : 0);
   if (dev < 0 || dev >= 64 || !configured[dev][qi]) {
     if (check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, PfSmem::kTotal), "cudaFuncSetAttribute(prefill smem)"))
+      return B200ATTN_ECUDA;
+    if (kPfCtasPerSm > 1 &&
+        check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared),
+                   "cudaFuncSetAttribute(prefill carveout)"))
       return B200ATTN_ECUDA;
     if (dev >= 0 && dev < 64) configured[dev][qi] = true;
   }

@@ -58,6 +58,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--json", default=None)
     ap.add_argument("--only", default=None)
+    ap.add_argument("--ours-only", action="store_true", help="skip the comparison arms (ncu captures)")
     a = ap.parse_args()
     dev = torch.device("cuda")
     ks = torch.tensor([4.5 / 448.0], device=dev); vs = torch.tensor([4.5 / 448.0], device=dev)
@@ -90,6 +91,10 @@ def main():
 
         us, _ = _graph_time(ours, 1)
         row["ours"] = {"us": us, "tflops": P["flops"] / us / 1e6}
+        if a.ours_only:
+            res[name] = row
+            print(name, json.dumps(row), flush=True)
+            continue
         # ---- vLLM Triton unified_attention ----
         try:
             from vllm.v1.attention.ops.triton_unified_attention import unified_attention

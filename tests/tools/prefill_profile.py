@@ -44,3 +44,12 @@ print(f"  CTA total            {np.mean(w[:, 12] / n):8.0f}")
 for lbl, k in (("softmax: wait S", 0), ("softmax: wait P free", 1), ("softmax: exchange bar", 2), ("producer: wait K slot", 4),
                ("producer: wait V slot", 5), ("mma: wait K tile", 8), ("mma: wait S free", 9), ("mma: wait V tile", 10), ("mma: wait P ready", 11)):
     print(f"  {lbl:22s} {np.mean(w[:, k] / n):8.0f}")
+# per-CTA fixed cost vs per-tile cost: least-squares line through (kv tiles, CTA cycles) over every CTA that had work
+allw = d[d[:, 13] > 0]
+A = np.stack([np.ones(len(allw)), allw[:, 14]], axis=1)
+(a_fix, b_tile), *_ = np.linalg.lstsq(A, allw[:, 12], rcond=None)
+print(f"  fit over {len(allw)} CTAs: cycles = {a_fix:.0f} + {b_tile:.0f} x kv tiles   (sum of CTA cycles / 148 SMs = {allw[:, 12].sum() / 148:.0f})")
+for lo, hi in ((1, 2), (4, 5), (16, 17), (32, 33), (63, 65)):
+    sel = allw[(allw[:, 14] >= lo) & (allw[:, 14] < hi)]
+    if len(sel):
+        print(f"    CTAs with {lo}-{hi - 1} kv tiles: {len(sel):4d}, mean cycles {sel[:, 12].mean():8.0f}")
