@@ -41,13 +41,22 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int n, int iters
   const uint32_t tmem = tmem_ptr;
   if ((int)blockIdx.x < ctas_active && threadIdx.x == 0) {
     const uint32_t idesc = (1u << 4) | (((uint32_t)n >> 3) << 17) | ((128u >> 4) << 24) | ((mode & 2) ? (1u << 16) : 0u);
+    // descriptors precomputed, four MMAs per trip: the single issuing thread must not be the limit
+    uint64_t da[4], db[4];
+    uint32_t ta[4];
+    for (int k = 0; k < 4; ++k) {
+      da[k] = desc_sw128(base + k * 32, 16, 1024);
+      db[k] = (mode & 2) ? desc_sw128(base + 32768 + k * 4096, 0, 1024) : desc_sw128(base + 32768 + k * 32, 16, 1024);
+      ta[k] = tmem + 448 + k * 8;
+    }
     const long long t0 = clock64();
-    for (int i = 0; i < iters; ++i) {
-      const int k = i & 3;
-      const uint32_t d = tmem + (uint32_t)((i / 8) % ndst) * (uint32_t)n;
-      const uint64_t db = (mode & 2) ? desc_sw128(base + 32768 + k * 4096, 0, 1024) : desc_sw128(base + 32768 + k * 32, 16, 1024);
-      if (mode & 1) mma_ts(d, tmem + 448 + k * 8, db, idesc, 1u);
-      else mma_ss(d, desc_sw128(base + k * 32, 16, 1024), db, idesc, 1u);
+    for (int i = 0; i < iters; i += 4) {
+      const uint32_t d = tmem + (uint32_t)((i >> 3) & (ndst - 1)) * (uint32_t)n;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (mode & 1) mma_ts(d, ta[k], db[k], idesc, 1u);
+        else mma_ss(d, da[k], db[k], idesc, 1u);
+      }
     }
     const long long t1 = clock64();
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
@@ -69,7 +78,7 @@ int main() {
   cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
   const int iters = 4096;
   for (int ctas : {1, 148})
-    for (int n : {128, 256})
+    for (int n : {16, 32, 64, 128, 256})
       for (int mode = 0; mode < 4; ++mode)
         for (int ndst : {1, 2}) {
           if (n == 256 && ndst == 2 && (mode & 1)) continue;   // A operand columns would overlap the accumulators
