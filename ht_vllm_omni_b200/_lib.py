@@ -14,7 +14,7 @@ TILE_TOKENS = 64
 MAX_GROUP = 16
 MAX_CTAS = 1024
 PEER_CTAS = 32
-ABI_VERSION = 7
+ABI_VERSION = 8
 DECODE_FUSED_MERGE = 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -53,6 +53,8 @@ PROTOTYPES = {
     "b200attn_workspace_bytes": (_sz, [_i32, _i32]),
     "b200attn_decode": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _p, _i32,
                                   _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32, _p, _sz, _p, _p, _i32, _i32, _p]),
+    "b200attn_decode_static": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _i64, _p, _i32,
+                                         _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32, _p]),
     "b200attn_decode_kv_write": (C.c_int, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _i64, _i64, _i64,
                                            _i64, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _p, _i32, _p, _i32,
                                            _p, _sz, _p, _p, _i32, _i32, _p]),

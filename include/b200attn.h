@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 7
+#define B200ATTN_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -304,6 +304,39 @@ B200ATTN_API int b200attn_decode_per_token_head(const void* q, int64_t q_stride_
                     void* workspace, size_t workspace_bytes,
                     float* lse_out /* nullable */, const int32_t* row_map /* nullable */,
                     int32_t fresh_tokens, int32_t flags, void* stream);
+
+/*
+ * Plan + split-KV paged decode WITHOUT caller-provided scratch and without any device allocation.
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Same result as b200attn_decode_plan followed by b200attn_decode(..., B200ATTN_DECODE_FUSED_MERGE) with
+ * row_map = NULL and num_ctas = min(b200attn_default_ctas(kv_dtype), B200ATTN_STATIC_MAX_CTAS); the caller still passes the
+ * inputs and `out` (and `lse_out`, nullable).  The plan buffer and the split-KV workspace live in ONE file-scope
+ * `static __device__` array inside the library (csrc/decode_static.cu; < 6 MiB, held by every GPU that loads the library
+ * until the process exits), whose device address is looked up once per device with cudaGetSymbolAddress.  The call performs
+ * no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limits: head_dim 128 only (B200ATTN_EINVAL otherwise); num_seqs <= B200ATTN_STATIC_MAX_SEQS (B200ATTN_ENOSPACE beyond, with
+ * a message naming the limit).  All other arguments, dtypes and alignment rules as b200attn_decode.
+ * Every call shares the array: nothing in it needs to survive between calls (the plan entries and merge counters are
+ * rewritten / zeroed by each call's plan kernel), and two calls that OVERLAP on the GPU -- different streams, or graph
+ * branches without an edge between them -- race on it.  Calls on one stream are ordered and safe.
+ */
+#define B200ATTN_STATIC_MAX_SEQS 1024   /* decode rows per call */
+#define B200ATTN_STATIC_MAX_CTAS 320    /* decode grid the static workspace is sized for (2 CTAs/SM on 148 SMs = 296) */
+B200ATTN_API int b200attn_decode_static(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+                    void* out, int64_t out_stride_t, int64_t out_stride_h,
+                    const void* k_cache, const void* v_cache,
+                    int64_t stride_block, int64_t stride_slot, int64_t stride_head,
+                    int64_t num_blocks,
+                    const int32_t* block_table, int64_t block_table_stride,
+                    const int32_t* seq_lens, int32_t num_seqs,
+                    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                    int32_t block_size, int32_t q_dtype, int32_t kv_dtype,
+                    float sm_scale, const float* k_scale, const float* v_scale,
+                    int32_t scale_stride,
+                    float* lse_out /* nullable, [num_seqs][num_q_heads] natural-log LSE */,
+                    int32_t fresh_tokens, void* stream);
 
 /*
  * Kernel 3 — merge of split-KV partials (online-softmax reduction with warp shuffles).

@@ -65,7 +65,7 @@ def test_only_sm100a_code_is_embedded():
 
 
 def test_version_and_geometry(lib):
-    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 7
+    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 8
     assert _lib.TILE_TOKENS == 64 and _lib.MAX_GROUP == 16
     assert lib.b200attn_plan_bytes(64) >= (8 + 1024 * 64 + 1024 * 4 + 65) * 4   # header, 256-byte CTA entries, merge counters, prefix
     assert lib.b200attn_plan_bytes(64) % 16 == 0

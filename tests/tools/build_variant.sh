@@ -11,7 +11,7 @@ obj="$root/build_variants/${name}_$(basename "$src" .cu).o"
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -fvisibility=hidden \
      --expt-relaxed-constexpr -cudart static -Xptxas -v "$@" -c "$src" -o "$obj" 2> "$root/build_variants/${name}.ptxas.log"
 objs=""
-for o in abi kv_write rope_kv_write kv_gather decode decode_tc decode_simt prefill_tc plan_merge peer_exchange; do
+for o in abi kv_write rope_kv_write kv_gather decode decode_tc decode_simt decode_static prefill_tc plan_merge peer_exchange; do
   if [ "$o" = "$(basename "$src" .cu)" ]; then objs="$objs $obj"; else objs="$objs $o.o"; fi
 done
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -cudart static -o "$root/build_variants/${name}.so" $objs
