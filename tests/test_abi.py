@@ -120,3 +120,14 @@ def test_product_package_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
                 assert "liboracle" not in text, f
+
+
+def test_decode_static_refuses_oversize_requests_before_touching_the_device(lib):
+    """b200attn_decode_static validates against the static array's limits first: no device is needed to be told no."""
+    def call(num_seqs, head_dim):
+        return lib.b200attn_decode_static(None, 0, 0, None, 0, 0, None, None, 0, 0, 0, 1, None, 0, None, num_seqs, 16, 2, head_dim, 16,
+                                          _lib.DT_BF16, _lib.DT_FP8_E4M3, 1.0, None, None, 0, None, -1, None)
+
+    assert call(1025, 128) == -3 and b"1024" in lib.b200attn_last_error()      # B200ATTN_ENOSPACE, names the limit
+    assert call(8, 64) == -1 and b"head_dim" in lib.b200attn_last_error()      # B200ATTN_EINVAL
+    assert call(0, 128) == 0                                                   # empty batch: nothing to do
